@@ -1,0 +1,200 @@
+/*
+ * mcmc_b200.h — C ABI of the B200-native sampling hot path.
+ *
+ * The reference (Chuxuan-a/mcmc) is pure Python/JAX and has no FFI of its own;
+ * the drop-in boundary is therefore the call signature of its four *_run
+ * functions.  Each entry point below replaces one of them and is what a
+ * jax.ffi / ctypes / cgo binding for that function would bind:
+ *
+ *   mcmc_hmc_run     <- samplers/HMC.py:223-314     (hmc_run; hmc_step :138-219; leapfrog :86-134)
+ *   mcmc_grahmc_run  <- samplers/GRAHMC.py:353-456  (rahmc_run; rahmc_step :265-349;
+ *                                                    _trajectory_with_schedule :215-261;
+ *                                                    _conformal_leapfrog_step :152-211;
+ *                                                    friction schedules :69-106)
+ *   mcmc_rwmh_run    <- samplers/RWMH.py:123-178    (rwMH_run; rwMH_step :73-119)
+ *   mcmc_nuts_run    <- samplers/NUTS.py:446-514    (nuts_run; nuts_step :399-442;
+ *                                                    _nuts_step_single_chain :202-396)
+ *   mcmc_target_eval <- vmap(jax.value_and_grad(log_prob_fn)) call sites
+ *                       HMC.py:73,123  GRAHMC.py:140,203  NUTS.py:77,111  RWMH.py:67,102
+ *                       over the closures of benchmarks/targets.py:38-482
+ *   mcmc_friction_table <- samplers/GRAHMC.py:69-106,193-194,246-252
+ *   mcmc_welford_finalize / mcmc_chain_moments <- tuning/adaptation.py:229-265
+ *                       (per-chain Welford, mean of per-chain variances) and
+ *                       tuning/welford.py:42-100
+ *
+ * Conventions
+ *  - plain C, POD structs, raw pointers and sizes; no torch / C++ types.
+ *  - every entry returns 0 on success, a negative MCMC_E* code otherwise;
+ *    mcmc_last_error() gives a thread-local message.  No exception crosses
+ *    the ABI.  There is NO CPU fallback: without a CUDA device every compute
+ *    entry fails with MCMC_ECUDA.
+ *  - *_run entries take DEVICE pointers, are asynchronous on `stream`
+ *    (a cudaStream_t passed as void*), allocate nothing and never sync the
+ *    host.  mcmc_run_host is the same path with HOST pointers (it owns the
+ *    H2D/D2H copies and a cached device arena).
+ *  - all arrays are row-major with the reference's shapes: samples (S,C,D),
+ *    log_probs (S,C), state (C,D) / (C,), everything fp64 except
+ *    accept_count (int32), accept_rate (float32), tree_depths (int32).
+ */
+#ifndef MCMC_B200_H_
+#define MCMC_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MCMC_ABI_VERSION 1
+
+/* error codes */
+#define MCMC_OK 0
+#define MCMC_EINVAL (-1)   /* bad argument (the reference's ValueError / KeyError) */
+#define MCMC_ECUDA (-2)    /* CUDA runtime failure or no device */
+#define MCMC_ENOTSUP (-3)  /* unsupported combination (e.g. D too large) */
+#define MCMC_EWORKSPACE (-4) /* workspace missing or too small */
+
+/* samplers */
+enum { MCMC_SAMPLER_HMC = 0, MCMC_SAMPLER_GRAHMC = 1, MCMC_SAMPLER_RWMH = 2, MCMC_SAMPLER_NUTS = 3 };
+
+/* targets: benchmarks/targets.py factories, in file order (+ a general dense Gaussian) */
+enum {
+  MCMC_TARGET_STANDARD_NORMAL = 0,   /* targets.py:50-52;  params[0]: 1 -> with the D*log(2pi) term (default), 0 -> README.md:51 variant */
+  MCMC_TARGET_CORRELATED_GAUSSIAN = 1, /* targets.py:79-98; params[0]=rho (closed form of the compound-symmetry precision) */
+  MCMC_TARGET_ILL_CONDITIONED = 2,   /* targets.py:125-137; params[0]=kappa */
+  MCMC_TARGET_NEALS_FUNNEL = 3,      /* targets.py:166-185 */
+  MCMC_TARGET_LOG_GAMMA = 4,         /* targets.py:236-251; params[0]=alpha, [1]=beta, [2]=lgamma(alpha)+alpha*log(beta) */
+  MCMC_TARGET_STUDENT_T = 5,         /* targets.py:300-311; params[0]=df, [1]=log normaliser per dim */
+  MCMC_TARGET_ROSENBROCK = 6,        /* targets.py:367-387; params[0]=scale (a = 1/scale^2) */
+  MCMC_TARGET_GAUSSIAN_MIXTURE = 7,  /* targets.py:432-454; params[0]=separation */
+  MCMC_TARGET_DENSE_GAUSSIAN = 8,    /* general x^T P x with P = buffers.cov_inv (D*D); params[0]=logdet(Sigma) */
+  MCMC_NUM_TARGETS = 9
+};
+
+/* friction schedules: samplers/GRAHMC.py:113-119 registry order */
+enum {
+  MCMC_SCHED_CONSTANT = 0, MCMC_SCHED_TANH = 1, MCMC_SCHED_SIGMOID = 2,
+  MCMC_SCHED_LINEAR = 3, MCMC_SCHED_SINE = 4, MCMC_NUM_SCHEDULES = 5
+};
+
+enum { MCMC_RNG_PHILOX = 0, MCMC_RNG_INJECTED = 1 };
+
+/* flags */
+#define MCMC_FLAG_TRACK_PROPOSALS 1u  /* HMC/GRAHMC: fill pre_q/pre_lp/prop_q/prop_lp/delta_h (HMC.py:287-305) */
+#define MCMC_FLAG_ACCUM_WELFORD 2u    /* update welford_mean/m2 with every stored sample (adaptation.py:229-235) */
+#define MCMC_FLAG_NO_SAMPLES 4u       /* do not store samples/log_probs (warmup batches only need the moments) */
+
+#define MCMC_MAX_DIM 128
+#define MCMC_MAX_TREE_DEPTH 20
+
+typedef struct McmcParams {
+  uint32_t abi_version;     /* MCMC_ABI_VERSION */
+  int32_t target_id;
+  int32_t schedule_id;      /* GRAHMC only */
+  int32_t rng_mode;
+  double target_params[8];
+  int64_t n_chains;         /* C: chains in THIS shard */
+  int64_t num_samples;      /* S */
+  int64_t burn_in;
+  int64_t chain_offset;     /* global index of this shard's first chain: Philox streams are keyed on
+                               chain_offset + local index, so results do not depend on the sharding */
+  int32_t n_dim;            /* D */
+  int32_t num_steps;        /* L (HMC/GRAHMC) */
+  int32_t max_tree_depth;   /* NUTS */
+  uint32_t flags;
+  double step_size;         /* epsilon (HMC/GRAHMC/NUTS); proposal scale (RWMH) */
+  double gamma;             /* GRAHMC friction amplitude */
+  double steepness;         /* GRAHMC tanh/sigmoid steepness */
+  double delta_max;         /* NUTS divergence threshold */
+  uint32_t seed[2];         /* Philox key (the reference's uint32[2] PRNG key) */
+  uint32_t reserved[2];
+} McmcParams;
+
+typedef struct McmcBuffers {
+  /* inputs */
+  const double* init_q;     /* [C*D] */
+  const double* inv_mass;   /* [D] diagonal of M^-1, NULL -> ones (HMC.py:264-265) */
+  const double* cov_inv;    /* [D*D], MCMC_TARGET_DENSE_GAUSSIAN only */
+  const double* z_inject;   /* [(burn+S)*C*D] standard normals, rng_mode INJECTED */
+  const double* u_inject;   /* [(burn+S)*C]   uniforms [0,1),   rng_mode INJECTED */
+  const double* nuts_dir_u; /* [(burn+S)*C*max_tree_depth] uniforms: direction=+1 iff u<0.5 (NUTS.py:255-256) */
+  const double* nuts_prop_u;/* [(burn+S)*C*max_tree_depth] uniforms for the proposal swap (NUTS.py:336) */
+  /* outputs (any may be NULL unless stated) */
+  double* samples;          /* [S*C*D] post-MH positions */
+  double* log_probs;        /* [S*C] */
+  int32_t* accept_count;    /* [C] */
+  float* accept_rate;       /* [C] = float(accept_count)/float(S) */
+  double* final_q;          /* [C*D] */
+  double* final_lp;         /* [C] */
+  double* final_g;          /* [C*D] (not RWMH) */
+  double* pre_q;            /* [S*C*D] tracking */
+  double* pre_lp;           /* [S*C] */
+  double* prop_q;           /* [S*C*D] */
+  double* prop_lp;          /* [S*C] */
+  double* delta_h;          /* [S*C] */
+  int32_t* tree_depths;     /* [S*C] NUTS */
+  double* mean_accept_probs;/* [S*C] NUTS */
+  /* in/out */
+  double* welford_mean;     /* [C*D] per-chain running mean  (MCMC_FLAG_ACCUM_WELFORD) */
+  double* welford_m2;       /* [C*D] per-chain running M2 */
+  double welford_count;     /* samples already folded into welford_* before this call */
+  /* device counters, fused in-kernel reductions (exact integer atomics):
+     [0] sum accept_count over chains, [1] sum of gradient evaluations,
+     [2] sum of tree depths (NUTS), [3] number of divergent transitions (NUTS) */
+  unsigned long long* counters; /* [4], zeroed by the callee at launch */
+  void* workspace;          /* mcmc_workspace_bytes() bytes of device scratch */
+  size_t workspace_bytes;
+} McmcBuffers;
+
+int mcmc_abi_version(void);
+const char* mcmc_last_error(void);
+/* number of CUDA devices usable by this library (0 -> every compute entry fails) */
+int mcmc_device_count(void);
+
+/* device scratch the sampler needs for these params (NUTS tree ends, friction table ...) */
+int mcmc_workspace_bytes(int sampler, const McmcParams* p, size_t* bytes);
+
+int mcmc_hmc_run(const McmcParams* p, const McmcBuffers* b, void* stream);
+int mcmc_grahmc_run(const McmcParams* p, const McmcBuffers* b, void* stream);
+int mcmc_rwmh_run(const McmcParams* p, const McmcBuffers* b, void* stream);
+int mcmc_nuts_run(const McmcParams* p, const McmcBuffers* b, void* stream);
+
+/* Same path with HOST pointers in McmcBuffers (workspace ignored): copies the
+   inputs to a cached device arena, runs the sampler on the library's own
+   stream, copies every non-NULL output back and synchronises.  `device` is the
+   CUDA ordinal. */
+int mcmc_run_host(int sampler, const McmcParams* p, const McmcBuffers* host, int device);
+/* free the cached arena of mcmc_run_host */
+int mcmc_host_arena_release(void);
+
+/* log p and grad log p of n points (device pointers; lp or grad may be NULL) */
+int mcmc_target_eval(const McmcParams* p, const double* cov_inv, const double* q,
+                     int64_t n, double* lp, double* grad, void* stream);
+
+/* s_i = exp(-gamma_i * eps/2), i = 0..L-1, written to a DEVICE array of L doubles
+   (and gamma_i to gamma_out if not NULL) */
+int mcmc_friction_table(int schedule_id, int num_steps, double step_size, double gamma,
+                        double steepness, double* s_out, double* gamma_out, void* stream);
+
+/* Cross-chain reductions used by the warmup (tuning/adaptation.py:238-265).
+   mcmc_welford_finalize: out[d] = sum_c m2[c,d]/(max(count,2)-1), d < D  (device pointers;
+   the caller divides by the global chain count after its all-reduce).
+   mcmc_chain_moments: per-chain mean/M2 over the S axis of samples (S,C,D), merged into
+   welford_mean/m2 exactly as S sequential welford_update calls would. */
+int mcmc_welford_finalize(const double* welford_m2, double count, int64_t n_chains, int32_t n_dim,
+                          double* out_sum_var, void* workspace, size_t workspace_bytes, void* stream);
+int mcmc_chain_moments(const double* samples, int64_t num_samples, int64_t n_chains, int32_t n_dim,
+                       double* welford_mean, double* welford_m2, double count_before, void* stream);
+/* deterministic sum of n doubles -> out[0] (device pointers) */
+int mcmc_sum_f64(const double* x, int64_t n, double* out, void* workspace, size_t workspace_bytes,
+                 void* stream);
+
+/* register-resident DFMA throughput probe used as the fp64 roofline denominator:
+   runs `iters` dependent-chain FMA rounds on every SM and returns flop count and ms */
+int mcmc_fp64_peak_probe(int iters, double* flops_out, float* ms_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCMC_B200_H_ */
