@@ -83,8 +83,14 @@ EXPORTS = [
     "mcmc_welford_finalize", "mcmc_chain_moments", "mcmc_sum_f64", "mcmc_fp64_peak_probe",
 ]
 
-_LIB = None
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libmcmc_b200.so")
+_LIBS: dict = {}
+_CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
+LIB_PATHS = {
+    "fast": os.path.join(_CSRC, "libmcmc_b200.so"),
+    # same sources, -DMCMC_FAITHFUL -fmad=false: the reference's operation order, one rounding per op
+    "strict": os.path.join(_CSRC, "libmcmc_b200_strict.so"),
+}
+LIB_PATH = LIB_PATHS["fast"]
 
 
 class McmcError(RuntimeError):
@@ -93,16 +99,21 @@ class McmcError(RuntimeError):
         self.code = code
 
 
-def lib() -> C.CDLL:
-    """Load libmcmc_b200.so (built by __graft_entry__.build()); raise if absent."""
-    global _LIB
-    if _LIB is not None:
-        return _LIB
-    if not os.path.exists(LIB_PATH):
+def default_variant() -> str:
+    return "strict" if os.environ.get("MCMC_B200_STRICT", "0") not in ("", "0") else "fast"
+
+
+def lib(variant: str | None = None) -> C.CDLL:
+    """Load libmcmc_b200[_strict].so (built by __graft_entry__.build()); raise if absent."""
+    variant = variant or default_variant()
+    if variant in _LIBS:
+        return _LIBS[variant]
+    path = LIB_PATHS[variant]
+    if not os.path.exists(path):
         raise ImportError(
-            f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
             "(there is no CPU fallback)")
-    L = C.CDLL(LIB_PATH)
+    L = C.CDLL(path)
     L.mcmc_abi_version.restype = C.c_int
     L.mcmc_last_error.restype = C.c_char_p
     L.mcmc_device_count.restype = C.c_int
@@ -118,11 +129,15 @@ def lib() -> C.CDLL:
     L.mcmc_fp64_peak_probe.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_float), _P]
     if L.mcmc_abi_version() != ABI_VERSION:
         raise ImportError(f"ABI mismatch: library {L.mcmc_abi_version()} vs python {ABI_VERSION}")
-    _LIB = L
+    _LIBS[variant] = L
     return L
 
 
-def check(rc: int) -> None:
+def check(rc: int, variant: str | None = None) -> None:
+    """Map a non-zero return code to the exception the reference would raise."""
     if rc != 0:
-        msg = lib().mcmc_last_error()
-        raise McmcError(rc, msg.decode() if msg else "")
+        msg = lib(variant).mcmc_last_error()
+        text = msg.decode() if msg else ""
+        if rc == EINVAL:
+            raise ValueError(text)
+        raise McmcError(rc, text)

@@ -1,0 +1,416 @@
+// abi.cu — the extern "C" boundary declared in include/mcmc_b200.h: argument
+// validation (the reference's ValueError / KeyError cases), per-target dispatch,
+// the cross-chain reduction kernels of the warmup, the host-pointer entry and
+// the fp64 peak probe.  No exception crosses this file; no CPU compute path exists.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+#include "hmc_kernel.cuh"
+
+namespace mcmc {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+size_t nuts_workspace_bytes(const McmcParams& p) {
+  if (p.n_dim == 20 || p.n_dim == 10) return 0;  // tree ends live in shared memory
+  const size_t cpad = ((size_t)p.n_chains + 63) / 64 * 64;
+  return (size_t)8 * p.n_dim * cpad * sizeof(double);
+}
+
+#define MCMC_DECL(T)                                                                                   \
+  template <> int launch_hmc<T>(const Launch&, bool);                                                  \
+  template <> int launch_rwmh<T>(const Launch&);                                                       \
+  template <> int launch_nuts<T>(const Launch&);                                                       \
+  template <> int launch_target_eval<T>(const McmcParams&, const double*, const double*, int64_t,      \
+                                        double*, double*, cudaStream_t);
+MCMC_DECL(0) MCMC_DECL(1) MCMC_DECL(2) MCMC_DECL(3) MCMC_DECL(4) MCMC_DECL(5) MCMC_DECL(6) MCMC_DECL(7) MCMC_DECL(8)
+#undef MCMC_DECL
+
+typedef int (*HmcFn)(const Launch&, bool);
+typedef int (*RunFn)(const Launch&);
+typedef int (*EvalFn)(const McmcParams&, const double*, const double*, int64_t, double*, double*, cudaStream_t);
+static const HmcFn kHmc[MCMC_NUM_TARGETS] = {launch_hmc<0>, launch_hmc<1>, launch_hmc<2>, launch_hmc<3>, launch_hmc<4>,
+                                             launch_hmc<5>, launch_hmc<6>, launch_hmc<7>, launch_hmc<8>};
+static const RunFn kRwmh[MCMC_NUM_TARGETS] = {launch_rwmh<0>, launch_rwmh<1>, launch_rwmh<2>, launch_rwmh<3>, launch_rwmh<4>,
+                                              launch_rwmh<5>, launch_rwmh<6>, launch_rwmh<7>, launch_rwmh<8>};
+static const RunFn kNuts[MCMC_NUM_TARGETS] = {launch_nuts<0>, launch_nuts<1>, launch_nuts<2>, launch_nuts<3>, launch_nuts<4>,
+                                              launch_nuts<5>, launch_nuts<6>, launch_nuts<7>, launch_nuts<8>};
+static const EvalFn kEval[MCMC_NUM_TARGETS] = {launch_target_eval<0>, launch_target_eval<1>, launch_target_eval<2>,
+                                               launch_target_eval<3>, launch_target_eval<4>, launch_target_eval<5>,
+                                               launch_target_eval<6>, launch_target_eval<7>, launch_target_eval<8>};
+
+static int have_device() {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }
+  return n;
+}
+
+static int validate(const McmcParams* p, const McmcBuffers* b, int sampler) {
+  if (!p || !b) { set_error("null params/buffers"); return MCMC_EINVAL; }
+  if (p->abi_version != MCMC_ABI_VERSION) { set_error("abi_version %u != %d", p->abi_version, MCMC_ABI_VERSION); return MCMC_EINVAL; }
+  if (p->target_id < 0 || p->target_id >= MCMC_NUM_TARGETS) { set_error("Unknown target id %d", p->target_id); return MCMC_EINVAL; }
+  if (p->n_dim < 1 || p->n_dim > MCMC_MAX_DIM) { set_error("n_dim %d outside [1, %d]", p->n_dim, MCMC_MAX_DIM); return MCMC_ENOTSUP; }
+  if (p->n_chains < 0 || p->num_samples < 0 || p->burn_in < 0) { set_error("negative size"); return MCMC_EINVAL; }
+  if (p->n_chains > 0 && !b->init_q) { set_error("init_q is NULL"); return MCMC_EINVAL; }
+  if (p->rng_mode != MCMC_RNG_PHILOX && p->rng_mode != MCMC_RNG_INJECTED) { set_error("bad rng_mode %d", p->rng_mode); return MCMC_EINVAL; }
+  if (p->rng_mode == MCMC_RNG_INJECTED && (p->burn_in + p->num_samples) > 0 && p->n_chains > 0) {
+    if (!b->z_inject || !b->u_inject) { set_error("rng_mode INJECTED needs z_inject and u_inject"); return MCMC_EINVAL; }
+    if (sampler == MCMC_SAMPLER_NUTS && p->max_tree_depth > 0 && (!b->nuts_dir_u || !b->nuts_prop_u)) {
+      set_error("rng_mode INJECTED needs nuts_dir_u and nuts_prop_u"); return MCMC_EINVAL;
+    }
+  }
+  if (p->target_id == MCMC_TARGET_DENSE_GAUSSIAN) {
+    if (!b->cov_inv) { set_error("dense_gaussian needs cov_inv"); return MCMC_EINVAL; }
+    if (p->n_dim > 64) { set_error("dense_gaussian supports n_dim <= 64"); return MCMC_ENOTSUP; }
+  }
+  if ((sampler == MCMC_SAMPLER_HMC || sampler == MCMC_SAMPLER_GRAHMC)) {
+    if (p->num_steps < 0 || p->num_steps > MCMC_MAX_STEPS) { set_error("num_steps %d outside [0, %d]", p->num_steps, MCMC_MAX_STEPS); return MCMC_ENOTSUP; }
+  }
+  if (sampler == MCMC_SAMPLER_GRAHMC && (p->schedule_id < 0 || p->schedule_id >= MCMC_NUM_SCHEDULES)) {
+    set_error("Unknown friction schedule id %d", p->schedule_id); return MCMC_EINVAL;  // KeyError, GRAHMC.py:122
+  }
+  if (sampler == MCMC_SAMPLER_NUTS && (p->max_tree_depth < 0 || p->max_tree_depth > MCMC_MAX_TREE_DEPTH)) {
+    set_error("max_tree_depth %d outside [0, %d]", p->max_tree_depth, MCMC_MAX_TREE_DEPTH); return MCMC_EINVAL;
+  }
+  if (p->burn_in + p->num_samples > 0xffffffffLL) { set_error("more than 2^32 iterations per call"); return MCMC_ENOTSUP; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  return MCMC_OK;
+}
+
+static int run_device(int sampler, const McmcParams* p, const McmcBuffers* b, cudaStream_t stream) {
+  if (int rc = validate(p, b, sampler)) return rc;
+  Launch l;
+  l.p = *p;
+  l.b = *b;
+  l.stream = stream;
+  if (b->counters)
+    if (int rc = cuda_fail(cudaMemsetAsync(b->counters, 0, 4 * sizeof(unsigned long long), stream), "memset counters"))
+      return rc;
+  switch (sampler) {
+    case MCMC_SAMPLER_HMC: return kHmc[p->target_id](l, false);
+    case MCMC_SAMPLER_GRAHMC: return kHmc[p->target_id](l, true);
+    case MCMC_SAMPLER_RWMH: return kRwmh[p->target_id](l);
+    case MCMC_SAMPLER_NUTS: return kNuts[p->target_id](l);
+  }
+  set_error("Unknown sampler: %d", sampler);  // ValueError, adaptation.py:212
+  return MCMC_EINVAL;
+}
+
+// ------------------------------------------------------------------ reductions
+
+// out[d] = sum_c m2[c,d] / (max(count,2) - 1): one block per dimension slice, fixed-order
+// tree -> deterministic (tuning/welford.py:97-99, adaptation.py:240-248)
+__global__ void __launch_bounds__(256) welford_finalize_kernel(const double* __restrict__ m2, double denom, int64_t C,
+                                                               int D, double* __restrict__ partial) {
+  // grid = (nblk, 1); each block sums a contiguous range of chains for all D, writes partial[blk*D + d]
+  __shared__ double sh[256];
+  const int64_t per = (C + gridDim.x - 1) / gridDim.x;
+  const int64_t c0 = (int64_t)blockIdx.x * per;
+  const int64_t c1 = c0 + per < C ? c0 + per : C;
+  for (int d = 0; d < D; ++d) {
+    double s = 0.0;
+    for (int64_t c = c0 + threadIdx.x; c < c1; c += blockDim.x) s += m2[c * D + d] / denom;
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) partial[(size_t)blockIdx.x * D + d] = sh[0];
+    __syncthreads();
+  }
+}
+
+__global__ void sum_partials_kernel(const double* __restrict__ partial, int nblk, int D, double* __restrict__ out) {
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= D) return;
+  double s = 0.0;
+  for (int b = 0; b < nblk; ++b) s += partial[(size_t)b * D + d];
+  out[d] = s;
+}
+
+__global__ void __launch_bounds__(256) sum_f64_kernel(const double* __restrict__ x, int64_t n, double* __restrict__ partial) {
+  __shared__ double sh[256];
+  const int64_t per = (n + gridDim.x - 1) / gridDim.x;
+  const int64_t i0 = (int64_t)blockIdx.x * per;
+  const int64_t i1 = i0 + per < n ? i0 + per : n;
+  double s = 0.0;
+  for (int64_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) s += x[i];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
+}
+
+// per-chain sequential Welford over the S axis of samples (S, C, D): thread = (chain, dim) pair,
+// consecutive threads read consecutive addresses of one sample slab (coalesced).
+__global__ void __launch_bounds__(256) chain_moments_kernel(const double* __restrict__ samples, int64_t S, int64_t CD,
+                                                            double* __restrict__ mean, double* __restrict__ m2,
+                                                            double count_before) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= CD) return;
+  double mu = mean[i], mm = m2[i], cnt = count_before;
+  for (int64_t s = 0; s < S; ++s) {
+    const double x = samples[s * CD + i];
+    cnt += 1.0;
+    const double delta = x - mu;
+    mu = mu + delta / cnt;
+    mm = mm + delta * (x - mu);
+  }
+  mean[i] = mu;
+  m2[i] = mm;
+}
+
+__global__ void friction_table_kernel(int sched, int L, double eps, double gam, double steep, double* s_out,
+                                      double* gamma_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= L) return;
+  const double gi = friction_gamma_dev(sched, i * eps, eps * L, gam, steep);
+  if (gamma_out) gamma_out[i] = gi;
+  s_out[i] = exp(-gi * (0.5 * eps));
+}
+
+// fp64 roofline denominator: 8 independent FMA chains per thread, registers only
+__global__ void __launch_bounds__(256) fp64_probe_kernel(int iters, double* sink) {
+  double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double m = 0.999999, c = 1e-6;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+      a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+    }
+  }
+  const double s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+  if (s == 123.456) sink[0] = s;
+}
+
+// ------------------------------------------------------------------ host arena (mcmc_run_host)
+
+struct Arena {
+  std::mutex mu;
+  int device = -1;
+  char* base = nullptr;
+  size_t cap = 0;
+  cudaStream_t stream = nullptr;
+};
+static Arena g_arena;
+
+static int arena_reserve(int device, size_t bytes) {
+  if (g_arena.device != device || g_arena.cap < bytes) {
+    if (g_arena.base) { cudaSetDevice(g_arena.device); cudaFree(g_arena.base); g_arena.base = nullptr; g_arena.cap = 0; }
+    if (int rc = cuda_fail(cudaSetDevice(device), "cudaSetDevice")) return rc;
+    if (g_arena.stream && g_arena.device != device) { cudaStreamDestroy(g_arena.stream); g_arena.stream = nullptr; }
+    const size_t want = bytes + (bytes >> 3) + (1u << 20);
+    if (int rc = cuda_fail(cudaMalloc(&g_arena.base, want), "cudaMalloc(host arena)")) return rc;
+    g_arena.cap = want;
+    g_arena.device = device;
+  }
+  if (!g_arena.stream)
+    if (int rc = cuda_fail(cudaStreamCreateWithFlags(&g_arena.stream, cudaStreamNonBlocking), "cudaStreamCreate")) return rc;
+  return MCMC_OK;
+}
+
+}  // namespace mcmc
+
+using namespace mcmc;
+
+extern "C" {
+
+int mcmc_abi_version(void) { return MCMC_ABI_VERSION; }
+const char* mcmc_last_error(void) { return g_err; }
+int mcmc_device_count(void) { return have_device(); }
+
+int mcmc_workspace_bytes(int sampler, const McmcParams* p, size_t* bytes) {
+  if (!p || !bytes) { set_error("null argument"); return MCMC_EINVAL; }
+  *bytes = (sampler == MCMC_SAMPLER_NUTS) ? nuts_workspace_bytes(*p) : 0;
+  return MCMC_OK;
+}
+
+int mcmc_hmc_run(const McmcParams* p, const McmcBuffers* b, void* stream) {
+  return run_device(MCMC_SAMPLER_HMC, p, b, (cudaStream_t)stream);
+}
+int mcmc_grahmc_run(const McmcParams* p, const McmcBuffers* b, void* stream) {
+  return run_device(MCMC_SAMPLER_GRAHMC, p, b, (cudaStream_t)stream);
+}
+int mcmc_rwmh_run(const McmcParams* p, const McmcBuffers* b, void* stream) {
+  return run_device(MCMC_SAMPLER_RWMH, p, b, (cudaStream_t)stream);
+}
+int mcmc_nuts_run(const McmcParams* p, const McmcBuffers* b, void* stream) {
+  return run_device(MCMC_SAMPLER_NUTS, p, b, (cudaStream_t)stream);
+}
+
+int mcmc_target_eval(const McmcParams* p, const double* cov_inv, const double* q, int64_t n, double* lp, double* grad,
+                     void* stream) {
+  if (!p || (!q && n > 0)) { set_error("null argument"); return MCMC_EINVAL; }
+  if (p->target_id < 0 || p->target_id >= MCMC_NUM_TARGETS) { set_error("Unknown target id %d", p->target_id); return MCMC_EINVAL; }
+  if (p->n_dim < 1 || p->n_dim > MCMC_MAX_DIM) { set_error("n_dim %d outside [1, %d]", p->n_dim, MCMC_MAX_DIM); return MCMC_ENOTSUP; }
+  if (p->target_id == MCMC_TARGET_DENSE_GAUSSIAN && (!cov_inv || p->n_dim > 64)) { set_error("dense_gaussian needs cov_inv, n_dim <= 64"); return MCMC_EINVAL; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  return kEval[p->target_id](*p, cov_inv, q, n, lp, grad, (cudaStream_t)stream);
+}
+
+int mcmc_friction_table(int schedule_id, int num_steps, double step_size, double gamma, double steepness, double* s_out,
+                        double* gamma_out, void* stream) {
+  if (schedule_id < 0 || schedule_id >= MCMC_NUM_SCHEDULES) { set_error("Unknown friction schedule id %d", schedule_id); return MCMC_EINVAL; }
+  if (num_steps < 0 || !s_out) { set_error("bad argument"); return MCMC_EINVAL; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  if (num_steps == 0) return MCMC_OK;
+  friction_table_kernel<<<(num_steps + 127) / 128, 128, 0, (cudaStream_t)stream>>>(schedule_id, num_steps, step_size, gamma,
+                                                                                   steepness, s_out, gamma_out);
+  return cuda_fail(cudaGetLastError(), "friction_table launch");
+}
+
+#define MCMC_REDUCE_BLOCKS 256
+
+int mcmc_welford_finalize(const double* welford_m2, double count, int64_t n_chains, int32_t n_dim, double* out_sum_var,
+                          void* workspace, size_t workspace_bytes, void* stream) {
+  if (!welford_m2 || !out_sum_var || n_dim < 1) { set_error("bad argument"); return MCMC_EINVAL; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  const size_t need = (size_t)MCMC_REDUCE_BLOCKS * n_dim * sizeof(double);
+  if (!workspace || workspace_bytes < need) { set_error("welford_finalize needs %zu workspace bytes", need); return MCMC_EWORKSPACE; }
+  const double n = count > 2.0 ? count : 2.0;
+  welford_finalize_kernel<<<MCMC_REDUCE_BLOCKS, 256, 0, (cudaStream_t)stream>>>(welford_m2, n - 1.0, n_chains, n_dim,
+                                                                               (double*)workspace);
+  sum_partials_kernel<<<(n_dim + 127) / 128, 128, 0, (cudaStream_t)stream>>>((const double*)workspace, MCMC_REDUCE_BLOCKS,
+                                                                             n_dim, out_sum_var);
+  return cuda_fail(cudaGetLastError(), "welford_finalize launch");
+}
+
+int mcmc_chain_moments(const double* samples, int64_t num_samples, int64_t n_chains, int32_t n_dim, double* welford_mean,
+                       double* welford_m2, double count_before, void* stream) {
+  if (!samples || !welford_mean || !welford_m2) { set_error("null argument"); return MCMC_EINVAL; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  const int64_t CD = n_chains * n_dim;
+  if (CD == 0) return MCMC_OK;
+  chain_moments_kernel<<<(unsigned)((CD + 255) / 256), 256, 0, (cudaStream_t)stream>>>(samples, num_samples, CD, welford_mean,
+                                                                                      welford_m2, count_before);
+  return cuda_fail(cudaGetLastError(), "chain_moments launch");
+}
+
+int mcmc_sum_f64(const double* x, int64_t n, double* out, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!x || !out) { set_error("null argument"); return MCMC_EINVAL; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  const size_t need = (size_t)MCMC_REDUCE_BLOCKS * sizeof(double);
+  if (!workspace || workspace_bytes < need) { set_error("sum_f64 needs %zu workspace bytes", need); return MCMC_EWORKSPACE; }
+  sum_f64_kernel<<<MCMC_REDUCE_BLOCKS, 256, 0, (cudaStream_t)stream>>>(x, n, (double*)workspace);
+  sum_partials_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((const double*)workspace, MCMC_REDUCE_BLOCKS, 1, out);
+  return cuda_fail(cudaGetLastError(), "sum_f64 launch");
+}
+
+int mcmc_fp64_peak_probe(int iters, double* flops_out, float* ms_out, void* stream) {
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  int dev = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int blocks = sms * 8, threads = 256;
+  double* sink = nullptr;
+  if (int rc = cuda_fail(cudaMalloc(&sink, sizeof(double)), "cudaMalloc")) return rc;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  cudaStream_t s = (cudaStream_t)stream;
+  fp64_probe_kernel<<<blocks, threads, 0, s>>>(iters / 8 + 1, sink);  // warm-up
+  cudaEventRecord(e0, s);
+  fp64_probe_kernel<<<blocks, threads, 0, s>>>(iters, sink);
+  cudaEventRecord(e1, s);
+  cudaError_t e = cudaEventSynchronize(e1);
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(sink);
+  if (int rc = cuda_fail(e, "fp64 probe")) return rc;
+  if (flops_out) *flops_out = 2.0 * 64.0 * (double)iters * (double)blocks * (double)threads;
+  if (ms_out) *ms_out = ms;
+  return MCMC_OK;
+}
+
+int mcmc_host_arena_release(void) {
+  std::lock_guard<std::mutex> lk(g_arena.mu);
+  if (g_arena.base) { cudaSetDevice(g_arena.device); cudaFree(g_arena.base); }
+  if (g_arena.stream) cudaStreamDestroy(g_arena.stream);
+  g_arena.base = nullptr; g_arena.cap = 0; g_arena.stream = nullptr; g_arena.device = -1;
+  return MCMC_OK;
+}
+
+int mcmc_run_host(int sampler, const McmcParams* p, const McmcBuffers* h, int device) {
+  if (int rc = validate(p, h, sampler)) return rc;
+  std::lock_guard<std::mutex> lk(g_arena.mu);
+  const size_t C = (size_t)p->n_chains, D = (size_t)p->n_dim, S = (size_t)p->num_samples;
+  const size_t T = (size_t)(p->burn_in + p->num_samples);
+  const size_t md = (size_t)(p->max_tree_depth > 0 ? p->max_tree_depth : 1);
+  struct Item { const void* hsrc; void* hdst; void** slot; size_t bytes; };
+  McmcBuffers d = *h;
+  std::vector<Item> items;
+  auto in = [&](const double* const& hp, const double*& dp, size_t n) {
+    if (hp) items.push_back({hp, nullptr, (void**)&dp, n * sizeof(double)});
+  };
+  auto out = [&](auto* const& hp, auto*& dp, size_t bytes, bool also_in = false) {
+    if (hp) items.push_back({also_in ? (const void*)hp : nullptr, (void*)hp, (void**)&dp, bytes});
+  };
+  in(h->init_q, d.init_q, C * D);
+  in(h->inv_mass, d.inv_mass, D);
+  in(h->cov_inv, d.cov_inv, D * D);
+  if (p->rng_mode == MCMC_RNG_INJECTED) {
+    in(h->z_inject, d.z_inject, T * C * D);
+    in(h->u_inject, d.u_inject, T * C);
+    if (sampler == MCMC_SAMPLER_NUTS) { in(h->nuts_dir_u, d.nuts_dir_u, T * C * md); in(h->nuts_prop_u, d.nuts_prop_u, T * C * md); }
+  } else {
+    d.z_inject = d.u_inject = d.nuts_dir_u = d.nuts_prop_u = nullptr;
+  }
+  const bool nos = (p->flags & MCMC_FLAG_NO_SAMPLES) != 0;
+  if (!nos) { out(h->samples, d.samples, S * C * D * 8); out(h->log_probs, d.log_probs, S * C * 8); }
+  else { d.samples = nullptr; d.log_probs = nullptr; }
+  out(h->accept_count, d.accept_count, C * 4);
+  out(h->accept_rate, d.accept_rate, C * 4);
+  out(h->final_q, d.final_q, C * D * 8);
+  out(h->final_lp, d.final_lp, C * 8);
+  if (sampler != MCMC_SAMPLER_RWMH) out(h->final_g, d.final_g, C * D * 8); else d.final_g = nullptr;
+  if ((p->flags & MCMC_FLAG_TRACK_PROPOSALS) && (sampler == MCMC_SAMPLER_HMC || sampler == MCMC_SAMPLER_GRAHMC)) {
+    out(h->pre_q, d.pre_q, S * C * D * 8); out(h->pre_lp, d.pre_lp, S * C * 8);
+    out(h->prop_q, d.prop_q, S * C * D * 8); out(h->prop_lp, d.prop_lp, S * C * 8);
+    out(h->delta_h, d.delta_h, S * C * 8);
+  } else { d.pre_q = d.pre_lp = d.prop_q = d.prop_lp = d.delta_h = nullptr; }
+  if (sampler == MCMC_SAMPLER_NUTS) { out(h->tree_depths, d.tree_depths, S * C * 4); out(h->mean_accept_probs, d.mean_accept_probs, S * C * 8); }
+  else { d.tree_depths = nullptr; d.mean_accept_probs = nullptr; }
+  if (p->flags & MCMC_FLAG_ACCUM_WELFORD) {
+    out(h->welford_mean, d.welford_mean, C * D * 8, true); out(h->welford_m2, d.welford_m2, C * D * 8, true);
+  } else { d.welford_mean = d.welford_m2 = nullptr; }
+  out(h->counters, d.counters, 4 * sizeof(unsigned long long));
+  size_t ws = (sampler == MCMC_SAMPLER_NUTS) ? nuts_workspace_bytes(*p) : 0;
+  size_t total = ws + 256;
+  for (auto& it : items) total += (it.bytes + 255) / 256 * 256;
+  if (int rc = arena_reserve(device, total)) return rc;
+  char* cur = g_arena.base;
+  cudaStream_t s = g_arena.stream;
+  for (auto& it : items) {
+    *it.slot = cur;
+    if (it.hsrc && it.bytes)
+      if (int rc = cuda_fail(cudaMemcpyAsync(cur, it.hsrc, it.bytes, cudaMemcpyHostToDevice, s), "H2D")) return rc;
+    cur += (it.bytes + 255) / 256 * 256;
+  }
+  d.workspace = ws ? cur : nullptr;
+  d.workspace_bytes = ws;
+  if (int rc = run_device(sampler, p, &d, s)) return rc;
+  for (auto& it : items)
+    if (it.hdst && it.bytes)
+      if (int rc = cuda_fail(cudaMemcpyAsync(it.hdst, *it.slot, it.bytes, cudaMemcpyDeviceToHost, s), "D2H")) return rc;
+  return cuda_fail(cudaStreamSynchronize(s), "mcmc_run_host sync");
+}
+
+}  // extern "C"

@@ -1,0 +1,86 @@
+"""Builds libmcmc_b200.so (fast) and libmcmc_b200_strict.so (reference operation order,
+no FMA contraction) in-tree with nvcc for sm_100a.  Called by __graft_entry__.build().
+
+One translation unit per (sampler family, target) so the targets compile in parallel;
+objects are cached under build/<variant>/ and rebuilt when any source or flag changes.
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+NUM_TARGETS = 9
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+BASE = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+        "-Xcompiler", "-fPIC"]
+VARIANTS = {
+    "fast": (["-fmad=true"], "libmcmc_b200.so"),
+    "strict": (["-DMCMC_FAITHFUL", "-fmad=false", "-prec-div=true", "-prec-sqrt=true"], "libmcmc_b200_strict.so"),
+}
+HEADERS = ["common.cuh", "philox.cuh", "targets.cuh", "rowstore.cuh", "hmc_kernel.cuh", "rwmh_kernel.cuh",
+           "nuts_kernel.cuh", os.path.join("..", "..", "include", "mcmc_b200.h")]
+
+
+def _units():
+    yield "abi.cu", None
+    for fam in ("hmc_inst.cu", "rwmh_inst.cu", "nuts_inst.cu"):
+        for t in range(NUM_TARGETS):
+            yield fam, t
+
+
+def _digest(flags) -> str:
+    h = hashlib.sha256(" ".join(flags).encode())
+    for f in sorted(os.listdir(HERE)):
+        if f.endswith((".cu", ".cuh")):
+            h.update(open(os.path.join(HERE, f), "rb").read())
+    h.update(open(os.path.join(HERE, "..", "..", "include", "mcmc_b200.h"), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def build(variants=("fast", "strict"), verbose=False, jobs=None) -> list[str]:
+    if not os.path.exists(NVCC):
+        raise RuntimeError(f"nvcc not found at {NVCC}")
+    jobs = jobs or max(1, (os.cpu_count() or 4))
+    outs = []
+    for var in variants:
+        vflags, libname = VARIANTS[var]
+        flags = BASE + vflags
+        tag = _digest(flags)
+        odir = os.path.join(HERE, "build", var)
+        os.makedirs(odir, exist_ok=True)
+        lib = os.path.join(HERE, libname)
+        stamp = os.path.join(odir, "digest.txt")
+        if os.path.exists(lib) and os.path.exists(stamp) and open(stamp).read().strip() == tag:
+            outs.append(lib)
+            continue
+
+        def compile_one(unit):
+            src, t = unit
+            obj = os.path.join(odir, src.replace(".cu", "") + ("" if t is None else f"_t{t}") + ".o")
+            cmd = [NVCC] + flags + (["-DMCMC_TID=%d" % t] if t is not None else []) + ["-c", os.path.join(HERE, src), "-o", obj]
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            if r.returncode != 0:
+                raise RuntimeError(f"nvcc failed for {src} t={t} [{var}]:\n{r.stdout}\n{r.stderr}")
+            if verbose and r.stderr.strip():
+                print(r.stderr, file=sys.stderr)
+            return obj
+
+        with ThreadPoolExecutor(max_workers=jobs) as ex:
+            objs = list(ex.map(compile_one, list(_units())))
+        cmd = [NVCC, "-shared", "-o", lib] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"link failed [{var}]:\n{r.stdout}\n{r.stderr}")
+        open(stamp, "w").write(tag)
+        outs.append(lib)
+    return outs
+
+
+if __name__ == "__main__":
+    vs = tuple(sys.argv[1:]) or ("fast", "strict")
+    for p in build(vs, verbose=True):
+        print(p)

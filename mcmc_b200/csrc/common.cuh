@@ -1,0 +1,61 @@
+// common.cuh — shared declarations of the CUDA side (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/mcmc_b200.h"
+
+// Two builds of the same sources:
+//   libmcmc_b200.so         fast: FMA contraction on, per-dimension constants folded
+//                           (eps*w), consecutive half-kicks merged.
+//   libmcmc_b200_strict.so  -DMCMC_FAITHFUL -fmad=false: the reference's operation order,
+//                           one rounding per jnp op; bit-comparable with the C oracle
+//                           (oracle/mcmc_oracle.c, -ffp-contract=off) up to libm differences.
+#ifdef MCMC_FAITHFUL
+#define MCMC_IS_FAITHFUL 1
+#else
+#define MCMC_IS_FAITHFUL 0
+#endif
+
+#define MCMC_DYN_MAXD MCMC_MAX_DIM
+#define MCMC_MAX_STEPS 2048  // friction table lives in shared memory
+
+namespace mcmc {
+
+constexpr double kLog2Pi = 1.8378770664093454836;
+constexpr double kPi = 3.14159265358979323846;
+constexpr double kTwoM53 = 1.1102230246251565404e-16;
+
+// thread-local error string (abi.cu)
+void set_error(const char* fmt, ...);
+
+struct Launch {
+  McmcParams p;
+  McmcBuffers b;
+  cudaStream_t stream;
+};
+
+// jnp.minimum propagates NaN; fmin() does not.
+__device__ __forceinline__ double min_nan(double a, double b) {
+  return (a != a) ? a : ((b != b) ? b : (a < b ? a : b));
+}
+
+// Per-target launchers, one explicit specialisation per translation unit
+// (hmc_inst.cu / rwmh_inst.cu / nuts_inst.cu compiled with -DMCMC_TID=k).
+template <int TID> int launch_hmc(const Launch& l, bool friction);
+template <int TID> int launch_rwmh(const Launch& l);
+template <int TID> int launch_nuts(const Launch& l);
+template <int TID> int launch_target_eval(const McmcParams& p, const double* cov_inv, const double* q,
+                                          int64_t n, double* lp, double* grad, cudaStream_t s);
+
+// workspace layouts (bytes), shared by the launchers and mcmc_workspace_bytes
+size_t nuts_workspace_bytes(const McmcParams& p);
+
+inline int cuda_fail(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return 0;
+  set_error("%s: %s", what, cudaGetErrorString(e));
+  return MCMC_ECUDA;
+}
+
+}  // namespace mcmc
