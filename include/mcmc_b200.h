@@ -151,6 +151,9 @@ int mcmc_abi_version(void);
 const char* mcmc_last_error(void);
 /* number of CUDA devices usable by this library (0 -> every compute entry fails) */
 int mcmc_device_count(void);
+/* make `device` current for this thread's calls into the library (the library links its own
+   CUDA runtime; a host framework's cudaSetDevice is not guaranteed to be seen by it) */
+int mcmc_set_device(int device);
 
 /* device scratch the sampler needs for these params (NUTS tree ends, friction table ...) */
 int mcmc_workspace_bytes(int sampler, const McmcParams* p, size_t* bytes);

@@ -234,6 +234,10 @@ extern "C" {
 int mcmc_abi_version(void) { return MCMC_ABI_VERSION; }
 const char* mcmc_last_error(void) { return g_err; }
 int mcmc_device_count(void) { return have_device(); }
+int mcmc_set_device(int device) {
+  if (device < 0 || device >= have_device()) { set_error("device %d not available", device); return MCMC_ECUDA; }
+  return cuda_fail(cudaSetDevice(device), "cudaSetDevice");
+}
 
 int mcmc_workspace_bytes(int sampler, const McmcParams* p, size_t* bytes) {
   if (!p || !bytes) { set_error("null argument"); return MCMC_EINVAL; }

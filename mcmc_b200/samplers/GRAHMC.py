@@ -1,0 +1,93 @@
+"""rahmc_run / rahmc_init and the friction-schedule registry with the reference's signatures
+(samplers/GRAHMC.py:69-122, 127-148, 353-456).
+
+The five schedule callables exist for API compatibility (identity against
+FRICTION_SCHEDULES selects the kernel's schedule id; calling one evaluates
+gamma(t) on the host exactly as the reference's formula).  The kernel builds the
+per-step table s_i = exp(-gamma_i*eps/2) in its prologue.
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, Dict, NamedTuple, Optional
+
+import torch
+
+from .. import _abi
+from ..benchmarks.targets import resolve_log_prob
+from ..runtime import run_sampler
+from .HMC import _pack, hmc_init
+
+
+class RAHMCState(NamedTuple):
+    """samplers/GRAHMC.py:49-53."""
+    position: torch.Tensor
+    log_prob: torch.Tensor
+    grad_log_prob: torch.Tensor
+    accept_count: torch.Tensor
+
+
+def constant_schedule(t, T, gamma, steepness=None):
+    return -gamma if t < T / 2 else +gamma
+
+
+def tanh_schedule(t, T, gamma_max, steepness=5.0):
+    return gamma_max * math.tanh(steepness * (2.0 * t / T - 1.0))
+
+
+def sigmoid_schedule(t, T, gamma_max, steepness=10.0):
+    return gamma_max * (2.0 / (1.0 + math.exp(-(steepness * (t / T - 0.5)))) - 1.0)
+
+
+def linear_schedule(t, T, gamma_max, steepness=None):
+    return -gamma_max + (2.0 * gamma_max * t / T)
+
+
+def sine_schedule(t, T, gamma_max, steepness=None):
+    return gamma_max * math.sin(math.pi * (t / T - 0.5))
+
+
+FRICTION_SCHEDULES: Dict[str, Callable] = {
+    "constant": constant_schedule,
+    "tanh": tanh_schedule,
+    "sigmoid": sigmoid_schedule,
+    "linear": linear_schedule,
+    "sine": sine_schedule,
+}
+
+
+def get_friction_schedule(schedule_type: str) -> Callable:
+    return FRICTION_SCHEDULES[schedule_type]  # KeyError for unknown names, like GRAHMC.py:122
+
+
+def _schedule_id(friction_schedule) -> int:
+    if friction_schedule is None:
+        return _abi.SCHEDULE_IDS["constant"]  # GRAHMC.py:395-396
+    if isinstance(friction_schedule, str):
+        get_friction_schedule(friction_schedule)
+        return _abi.SCHEDULE_IDS[friction_schedule]
+    for name, fn in FRICTION_SCHEDULES.items():
+        if fn is friction_schedule:
+            return _abi.SCHEDULE_IDS[name]
+    raise NotImplementedError(
+        "friction_schedule must be one of mcmc_b200.samplers.GRAHMC.FRICTION_SCHEDULES (or its name); "
+        "arbitrary Python schedules cannot be compiled into the kernel")
+
+
+def rahmc_init(init_position, log_prob_fn) -> RAHMCState:
+    return RAHMCState(*hmc_init(init_position, log_prob_fn))
+
+
+def rahmc_run(key, log_prob_fn, init_position, step_size: float, num_steps: int, gamma: float, steepness: float,
+              num_samples: int, burn_in: int = 0, inv_mass_matrix=None, friction_schedule=None,
+              track_proposals: bool = False, *, _inject: Optional[dict] = None, _variant: Optional[str] = None,
+              _chain_offset: int = 0):
+    """Run GRAHMC/RAHMC with parallel chains (same return layout as hmc_run)."""
+    tag = resolve_log_prob(log_prob_fn)
+    out = run_sampler(_abi.SAMPLER_GRAHMC, tag, init_position, key=key, step_size=float(step_size),
+                      num_steps=int(num_steps), gamma=float(gamma),
+                      steepness=float(steepness if steepness is not None else 1.0),  # GRAHMC.py:409
+                      schedule_id=_schedule_id(friction_schedule), num_samples=int(num_samples),
+                      burn_in=int(burn_in), inv_mass_matrix=inv_mass_matrix, track_proposals=bool(track_proposals),
+                      inject=_inject, variant=_variant, chain_offset=_chain_offset)
+    return _pack(out, RAHMCState, track_proposals)

@@ -1,0 +1,52 @@
+"""hmc_run / hmc_init with the reference's signatures (samplers/HMC.py:61-82, 223-314).
+
+The whole burn-in + sampling loop runs as one CUDA kernel launch
+(mcmc_b200/csrc/hmc_kernel.cuh); results are CUDA float64 tensors with the
+reference's shapes.
+"""
+from __future__ import annotations
+
+from typing import NamedTuple, Optional
+
+import torch
+
+from .. import _abi
+from ..benchmarks.targets import resolve_log_prob
+from ..runtime import ensure_batched, run_sampler, target_eval, to_device, _device
+
+
+class HMCState(NamedTuple):
+    """samplers/HMC.py:23-35."""
+    position: torch.Tensor       # (n_chains, n_dim) float64
+    log_prob: torch.Tensor       # (n_chains,) float64
+    grad_log_prob: torch.Tensor  # (n_chains, n_dim) float64
+    accept_count: torch.Tensor   # (n_chains,) int32
+
+
+def hmc_init(init_position, log_prob_fn) -> HMCState:
+    tag = resolve_log_prob(log_prob_fn)
+    pos, _ = ensure_batched(to_device(init_position, _device(getattr(init_position, "device", None)
+                                                             if getattr(init_position, "is_cuda", False) else None)))
+    lp, g = target_eval(tag, pos, want_grad=True)
+    return HMCState(pos, lp, g, torch.zeros(pos.shape[0], dtype=torch.int32, device=pos.device))
+
+
+def _pack(out, state_cls, track):
+    state = state_cls(out["final_q"], out["final_lp"], out["final_g"], out["accept_count"])
+    base = (out["samples"], out["log_probs"], out["accept_rate"], state)
+    if track:
+        return base + (out["pre_q"], out["pre_lp"], out["prop_q"], out["prop_lp"], out["delta_h"])
+    return base
+
+
+def hmc_run(key, log_prob_fn, init_position, step_size: float, num_steps: int, num_samples: int, burn_in: int = 0,
+            inv_mass_matrix=None, track_proposals: bool = False, *, _inject: Optional[dict] = None,
+            _variant: Optional[str] = None, _chain_offset: int = 0):
+    """Run HMC with parallel chains.  Returns (samples (S,C,D), log_probs (S,C), accept_rate (C,) f32,
+    final_state) and, with track_proposals, + (pre_positions, pre_lps, prop_positions, prop_lps, deltas_H)."""
+    tag = resolve_log_prob(log_prob_fn)
+    out = run_sampler(_abi.SAMPLER_HMC, tag, init_position, key=key, step_size=float(step_size),
+                      num_steps=int(num_steps), num_samples=int(num_samples), burn_in=int(burn_in),
+                      inv_mass_matrix=inv_mass_matrix, track_proposals=bool(track_proposals), inject=_inject,
+                      variant=_variant, chain_offset=_chain_offset)
+    return _pack(out, HMCState, track_proposals)
