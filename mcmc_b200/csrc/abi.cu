@@ -28,6 +28,21 @@ size_t nuts_workspace_bytes(const McmcParams& p) {
   return (size_t)8 * p.n_dim * cpad * sizeof(double);
 }
 
+size_t hmc_workspace_bytes(const McmcParams& p) {
+  // queue + flags + hand-off state (q, g, lp, acc) of the chunked scheduler in hmc_kernel.cuh
+  const size_t C = (size_t)p.n_chains, D = (size_t)p.n_dim;
+  const size_t flag_bytes = (((C + 31) / 32) * 4 + 255) / 256 * 256;
+  return 256 + flag_bytes + (2 * C * D + C) * sizeof(double) + C * sizeof(int) + 256;
+}
+
+int device_sm_count() {
+  static int sms[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+  if (sms[dev] == 0) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+  return sms[dev];
+}
+
 #define MCMC_DECL(T)                                                                                   \
   template <> int launch_hmc<T>(const Launch&, bool);                                                  \
   template <> int launch_rwmh<T>(const Launch&);                                                       \
@@ -241,7 +256,8 @@ int mcmc_set_device(int device) {
 
 int mcmc_workspace_bytes(int sampler, const McmcParams* p, size_t* bytes) {
   if (!p || !bytes) { set_error("null argument"); return MCMC_EINVAL; }
-  *bytes = (sampler == MCMC_SAMPLER_NUTS) ? nuts_workspace_bytes(*p) : 0;
+  *bytes = (sampler == MCMC_SAMPLER_NUTS) ? nuts_workspace_bytes(*p)
+           : (sampler == MCMC_SAMPLER_HMC || sampler == MCMC_SAMPLER_GRAHMC) ? hmc_workspace_bytes(*p) : 0;
   return MCMC_OK;
 }
 
@@ -396,7 +412,8 @@ int mcmc_run_host(int sampler, const McmcParams* p, const McmcBuffers* h, int de
     out(h->welford_mean, d.welford_mean, C * D * 8, true); out(h->welford_m2, d.welford_m2, C * D * 8, true);
   } else { d.welford_mean = d.welford_m2 = nullptr; }
   out(h->counters, d.counters, 4 * sizeof(unsigned long long));
-  size_t ws = (sampler == MCMC_SAMPLER_NUTS) ? nuts_workspace_bytes(*p) : 0;
+  size_t ws = (sampler == MCMC_SAMPLER_NUTS) ? nuts_workspace_bytes(*p)
+              : (sampler == MCMC_SAMPLER_HMC || sampler == MCMC_SAMPLER_GRAHMC) ? hmc_workspace_bytes(*p) : 0;
   size_t total = ws + 256;
   for (auto& it : items) total += (it.bytes + 255) / 256 * 256;
   if (int rc = arena_reserve(device, total)) return rc;

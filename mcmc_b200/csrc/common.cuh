@@ -41,6 +41,15 @@ __device__ __forceinline__ double min_nan(double a, double b) {
   return (a != a) ? a : ((b != b) ? b : (a < b ? a : b));
 }
 
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 // Per-target launchers, one explicit specialisation per translation unit
 // (hmc_inst.cu / rwmh_inst.cu / nuts_inst.cu compiled with -DMCMC_TID=k).
 template <int TID> int launch_hmc(const Launch& l, bool friction);
@@ -51,6 +60,8 @@ template <int TID> int launch_target_eval(const McmcParams& p, const double* cov
 
 // workspace layouts (bytes), shared by the launchers and mcmc_workspace_bytes
 size_t nuts_workspace_bytes(const McmcParams& p);
+size_t hmc_workspace_bytes(const McmcParams& p);
+int device_sm_count();
 
 inline int cuda_fail(cudaError_t e, const char* what) {
   if (e == cudaSuccess) return 0;

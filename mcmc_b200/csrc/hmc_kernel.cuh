@@ -11,6 +11,8 @@
 //                                        samplers/GRAHMC.py:246-261 / :190-211
 //   friction schedules samplers/GRAHMC.py:69-106 (table s_i = exp(-gamma_i*eps/2) built in the prologue)
 #pragma once
+#include <cstdlib>
+
 #include "common.cuh"
 #include "philox.cuh"
 #include "rowstore.cuh"
@@ -22,6 +24,16 @@ struct HmcKArgs {
   McmcParams p;
   McmcBuffers b;
   TargetCtx t;
+  // wave-balanced scheduling (see hmc_kernel): work items = (chain group, iteration chunk)
+  int n_groups;          // ceil(C / BLOCK)
+  int n_chunks;          // 1: one block owns a group for the whole run (no queue, no hand-off)
+  int chunk_iters;       // iterations per chunk
+  unsigned int* queue;   // [1]  next item
+  unsigned int* flags;   // [n_groups] chunks completed per group
+  double* ho_q;          // [C*D] hand-off state between chunks
+  double* ho_g;          // [C*D]
+  double* ho_lp;         // [C]
+  int* ho_acc;           // [C]
 };
 
 // gamma(t) of samplers/GRAHMC.py:69-106 with t = i*eps, T = eps*L (:246,251)
@@ -47,25 +59,22 @@ struct HmcSmem {
   __host__ __device__ size_t off_s() const { return 3 * (size_t)n; }                 // s_i
   __host__ __device__ size_t off_a() const { return off_s() + (size_t)L; }           // merged scale
   __host__ __device__ size_t off_b() const { return off_a() + (size_t)L; }           // merged kick coeff
-  __host__ __device__ size_t off_tab() const { return off_b() + (size_t)L; }
+  __host__ __device__ size_t off_logtab() const { return off_b() + (size_t)L; }
+  __host__ __device__ size_t off_tab() const { return off_logtab() + kRngTableDoubles; }
   __host__ __device__ size_t off_q() const { return ((off_tab() + (size_t)tabn + 1) / 2) * 2; }
   __host__ __device__ size_t off_g() const { return off_q() + (size_t)n * BLOCK; }
   __host__ __device__ size_t off_stage() const { return off_g() + (size_t)n * BLOCK; }
-  __host__ __device__ size_t total_doubles() const { return off_stage() + (staged ? 2 * (size_t)n * BLOCK : 0); }
+  __host__ __device__ size_t total_doubles() const { return off_stage(); }
 };
 
-template <int TID, int DS, bool FRICTION, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) hmc_kernel(const HmcKArgs a) {
+template <int TID, int DS, bool FRICTION, int BLOCK, int MINB = 1>
+__global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
   constexpr int N = DS > 0 ? DS : MCMC_DYN_MAXD;
   const int n = DS > 0 ? DS : a.p.n_dim;
   const int L = a.p.num_steps;
   const int64_t C = a.p.n_chains;
   const int64_t S = a.p.num_samples, B = a.p.burn_in;
   const int tid = threadIdx.x;
-  const int64_t chain0 = (int64_t)blockIdx.x * BLOCK;
-  const bool active = chain0 + tid < C;
-  const int64_t chain = active ? chain0 + tid : C - 1;  // tail threads shadow the last chain, write nothing
-  const int nvalid = (int)((C - chain0) < BLOCK ? (C - chain0) : BLOCK);
   const bool store = !(a.p.flags & MCMC_FLAG_NO_SAMPLES) && a.b.samples != nullptr;
   const bool track = (a.p.flags & MCMC_FLAG_TRACK_PROPOSALS) != 0;
   const bool do_w = (a.p.flags & MCMC_FLAG_ACCUM_WELFORD) && a.b.welford_mean && a.b.welford_m2;
@@ -105,6 +114,7 @@ __global__ void __launch_bounds__(BLOCK) hmc_kernel(const HmcKArgs a) {
     }
   }
   target_table_fill<TID>(a.t, n, sm_tab);
+  rng_table_fill(smem + lay.off_logtab());
   __syncthreads();
   if (FRICTION && !MCMC_IS_FAITHFUL) {
     // merged coefficients: between steps i and i+1,  p <- p*(s_i s_{i+1}) + g*(h s_i s_{i+1} + h)
@@ -116,33 +126,87 @@ __global__ void __launch_bounds__(BLOCK) hmc_kernel(const HmcKArgs a) {
     __syncthreads();
   }
 
-  TileWriter<DS, BLOCK> tw;
-  if (store) tw.init(smem + lay.off_stage(), n, nvalid, a.b.samples + chain0 * n);
+  // Work distribution.  With C chains and only (SMs x resident blocks) slots, equal-length blocks
+  // leave the last wave partly empty (65,536 chains = 1.73 waves of 256 threads/SM: 13% lost).  So a
+  // block does not own a group of chains for the whole run: the run is cut into iteration chunks,
+  // items (chunk c, group g) are handed out in chunk-major order from an atomic queue, and the state
+  // of a group travels between chunks through HBM.  An item waits (flags[g] >= c) only on an item
+  // that a resident block has already taken, so the wait always ends.  Philox counters are keyed on
+  // (global chain, absolute iteration): the result does not depend on who runs which item.
+  __shared__ unsigned int s_item;
+  double* my_q_base = sm_q;
+  double q[N], p[N], g[N];
+  const unsigned int n_items = (unsigned int)a.n_groups * (unsigned int)a.n_chunks;
+  for (;;) {
+  unsigned int item;
+  if (a.n_chunks == 1) {
+    item = blockIdx.x;
+    if (item >= n_items) break;
+  } else {
+    if (tid == 0) s_item = atomicAdd(a.queue, 1u);
+    __syncthreads();
+    item = s_item;
+    __syncthreads();
+    if (item >= n_items) break;
+  }
+  const int grp = (int)(item % (unsigned int)a.n_groups);
+  const int chunk = (int)(item / (unsigned int)a.n_groups);
+  const int64_t it_begin = (int64_t)chunk * a.chunk_iters;
+  const int64_t it_end = (it_begin + a.chunk_iters < B + S) ? it_begin + a.chunk_iters : B + S;
+  const bool last_chunk = chunk == a.n_chunks - 1;
+  const int64_t chain0 = (int64_t)grp * BLOCK;
+  const bool active = chain0 + tid < C;
+  const int64_t chain = active ? chain0 + tid : C - 1;  // tail threads shadow the last chain, write nothing
+  const int nvalid = (int)((C - chain0) < BLOCK ? (C - chain0) : BLOCK);
+
+  // sample rows leave straight from the row-major current-state tile sm_q (see below)
+  const bool bulk = store && ((((size_t)nvalid * n * sizeof(double)) & 15) == 0) &&
+                    ((((size_t)(a.b.samples + chain0 * n)) & 15) == 0) && ((((size_t)C * n * sizeof(double)) & 15) == 0);
 
   RngCtx rng;
   {
     const uint64_t gid = (uint64_t)(a.p.chain_offset + chain);
     rng.k0 = a.p.seed[0]; rng.k1 = a.p.seed[1];
     rng.gid_lo = (uint32_t)gid; rng.gid_hi = (uint32_t)(gid >> 32);
+    rng.logtab = smem + lay.off_logtab();
   }
 
+  // Current state of the chain: q row-major [tid][n] in shared memory (it doubles as the TMA source
+  // of the sample tile), g as [d][tid]; registers hold q/p/g only during a trajectory.
+  double* my_q = my_q_base + (size_t)tid * n;
+  double lp;
+  int acc;
+  if (chunk == 0) {
   // ---- hmc_init (HMC.py:71-82): value and gradient at the initial position
-  double q[N], p[N], g[N];
   {
     const double* src = a.b.init_q + chain * n;
 #pragma unroll
     for (int d = 0; d < n; ++d) q[d] = src[d];
   }
-  double lp = target_eval<TID, DS, true, true>(a.t, n, q, g, sm_tab);
+  lp = target_eval<TID, DS, true, true>(a.t, n, q, g, sm_tab);
+  acc = 0;
+  } else {
+    // ---- resume: wait for the previous chunk of this group, then fetch its state from HBM (L2)
+    if (tid == 0) {
+      while (ld_acquire_u32(a.flags + grp) < (unsigned int)chunk) __nanosleep(200);
+    }
+    __syncthreads();
+    const double* sq = a.ho_q + chain * n;
+    const double* sg = a.ho_g + chain * n;
 #pragma unroll
-  for (int d = 0; d < n; ++d) {
-    sm_q[d * BLOCK + tid] = q[d];
-    sm_g[d * BLOCK + tid] = g[d];
+    for (int d = 0; d < n; ++d) {
+      q[d] = __ldcg(sq + d);
+      g[d] = __ldcg(sg + d);
+    }
+    lp = __ldcg(a.ho_lp + chain);
+    acc = __ldcg(a.ho_acc + chain);
   }
-  int acc = 0;
-  double wcount = a.b.welford_count;
+  store_row<DS>(my_q, q, n);
+#pragma unroll
+  for (int d = 0; d < n; ++d) sm_g[d * BLOCK + tid] = g[d];
+  double wcount = a.b.welford_count + (double)((it_begin > B) ? (it_begin - B) : 0);
 
-  for (int64_t it = 0; it < B + S; ++it) {
+  for (int64_t it = it_begin; it < it_end; ++it) {
     if (it == B) acc = 0;  // HMC.py:276-282
     const int64_t si = it - B;
 
@@ -172,7 +236,10 @@ __global__ void __launch_bounds__(BLOCK) hmc_kernel(const HmcKArgs a) {
     }
     const double H0 = -lp + 0.5 * kin;
 
-    // ---- trajectory: registers q, g hold the current state on entry
+    // ---- trajectory from the current state (cached lp and g: no re-evaluation, HMC.py:179-192)
+    load_row<DS>(q, my_q, n);
+#pragma unroll
+    for (int d = 0; d < n; ++d) g[d] = sm_g[d * BLOCK + tid];
     double lpn = lp;
 #if MCMC_IS_FAITHFUL
     for (int i = 0; i < L; ++i) {
@@ -237,8 +304,8 @@ __global__ void __launch_bounds__(BLOCK) hmc_kernel(const HmcKArgs a) {
     double H1 = -lpn + 0.5 * kin1;
     if (!isfinite(H1)) H1 = 1e10;
     const double log_alpha = H0 - H1;
-    const double u = injected ? a.b.u_inject[(size_t)it * C + chain] : philox_accept_uniform(rng, (uint32_t)it);
-    const bool accept = log(u) < min_nan(0.0, log_alpha);
+    const double log_u = injected ? log(a.b.u_inject[(size_t)it * C + chain]) : philox_accept_log_uniform(rng, (uint32_t)it);
+    const bool accept = log_u < min_nan(0.0, log_alpha);
 
     if (track && si >= 0 && active) {  // HMC.py:287-305
       const size_t o = (size_t)si * C + chain;
@@ -247,50 +314,75 @@ __global__ void __launch_bounds__(BLOCK) hmc_kernel(const HmcKArgs a) {
       if (a.b.delta_h) a.b.delta_h[o] = H1 - H0;
       if (a.b.pre_lp) a.b.pre_lp[o] = lp;
       if (a.b.pre_q) {
-        double* dst = a.b.pre_q + o * n;
-#pragma unroll
-        for (int d = 0; d < n; ++d) dst[d] = sm_q[d * BLOCK + tid];
+        load_row<DS>(p, my_q, n);  // p is dead here
+        store_row<DS>(a.b.pre_q + o * n, p, n);
       }
     }
 
+    // the TMA copy of the previous iteration's tile must have drained sm_q before it is overwritten
+    if (bulk) {
+      if (tid == 0) bulk_wait_read<0>();
+      __syncthreads();
+    }
     if (accept) {  // HMC.py:209-212
+      store_row<DS>(my_q, q, n);
 #pragma unroll
-      for (int d = 0; d < n; ++d) {
-        sm_q[d * BLOCK + tid] = q[d];
-        sm_g[d * BLOCK + tid] = g[d];
-      }
+      for (int d = 0; d < n; ++d) sm_g[d * BLOCK + tid] = g[d];
       lp = lpn;
       acc += 1;
-    } else {
-#pragma unroll
-      for (int d = 0; d < n; ++d) {
-        q[d] = sm_q[d * BLOCK + tid];
-        g[d] = sm_g[d * BLOCK + tid];
-      }
     }
 
     if (si >= 0) {
       if (store) {
-        tw.put(q, a.b.samples + ((size_t)si * C + chain0) * n, active);
+        double* gtile = a.b.samples + ((size_t)si * C + chain0) * n;
+        if (bulk) {
+          fence_proxy_async_smem();
+          __syncthreads();
+          if (tid == 0) bulk_store_s2g(gtile, sm_q, (uint32_t)((size_t)nvalid * n * sizeof(double)));
+        } else if (active) {
+          if (!accept) load_row<DS>(q, my_q, n);
+          store_row<DS>(gtile + (size_t)tid * n, q, n);
+        }
         if (active && a.b.log_probs) a.b.log_probs[(size_t)si * C + chain] = lp;
       }
       if (do_w && active) {  // tuning/welford.py:42-59, one fold per stored sample (adaptation.py:229-235)
+        if (!accept) load_row<DS>(q, my_q, n);
         wcount += 1.0;
         double* wm = a.b.welford_mean + chain * n;
         double* w2 = a.b.welford_m2 + chain * n;
 #pragma unroll
         for (int d = 0; d < n; ++d) {
-          const double mean = wm[d];
+          const double mean = __ldcg(wm + d);  // L2: another SM may have run the previous chunk
           const double delta = q[d] - mean;
           const double mean2 = mean + delta / wcount;
-          wm[d] = mean2;
-          w2[d] = w2[d] + delta * (q[d] - mean2);
+          __stcg(wm + d, mean2);
+          __stcg(w2 + d, __ldcg(w2 + d) + delta * (q[d] - mean2));
         }
       }
     }
   }
-  if (store) tw.finish();
+  if (bulk && tid == 0) bulk_wait_all();
+  load_row<DS>(q, my_q, n);
+#pragma unroll
+  for (int d = 0; d < n; ++d) g[d] = sm_g[d * BLOCK + tid];
 
+  if (!last_chunk) {
+    // ---- hand the group's state to whoever takes its next chunk
+    if (active) {
+      double* dq = a.ho_q + chain * n;
+      double* dg = a.ho_g + chain * n;
+#pragma unroll
+      for (int d = 0; d < n; ++d) {
+        __stcg(dq + d, q[d]);
+        __stcg(dg + d, g[d]);
+      }
+      __stcg(a.ho_lp + chain, lp);
+      __stcg(a.ho_acc + chain, acc);
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) st_release_u32(a.flags + grp, (unsigned int)chunk + 1u);
+  } else {
   // ---- epilogue: final state, acceptance statistics
   if (active) {
     if (a.b.accept_count) a.b.accept_count[chain] = acc;
@@ -304,13 +396,17 @@ __global__ void __launch_bounds__(BLOCK) hmc_kernel(const HmcKArgs a) {
     unsigned int v = active ? (unsigned int)acc : 0u;
     v = __reduce_add_sync(0xffffffffu, v);
     if ((tid & 31) == 0 && v) atomicAdd(a.b.counters + 0, (unsigned long long)v);
-    if (blockIdx.x == 0 && tid == 0)
+    if (grp == 0 && tid == 0)
       atomicAdd(a.b.counters + 1, (unsigned long long)C * (unsigned long long)(B + S) * (unsigned long long)L);
   }
+  }
+  __syncthreads();  // sm_q / sm_g are rewritten by the next item
+  if (a.n_chunks == 1) break;
+  }  // item loop
 }
 
 // host-side launcher for one (target, D-variant)
-template <int TID, int DS, bool FRICTION, int BLOCK>
+template <int TID, int DS, bool FRICTION, int BLOCK, int MINB = 1>
 int launch_hmc_variant(const Launch& l) {
   HmcKArgs a;
   a.p = l.p;
@@ -320,7 +416,7 @@ int launch_hmc_variant(const Launch& l) {
   const bool store = !(l.p.flags & MCMC_FLAG_NO_SAMPLES) && l.b.samples != nullptr;
   const HmcSmem<DS, BLOCK> lay(n, l.p.num_steps, target_table_len(TID, n), store);
   const size_t smem = lay.total_doubles() * sizeof(double);
-  auto kern = hmc_kernel<TID, DS, FRICTION, BLOCK>;
+  auto kern = hmc_kernel<TID, DS, FRICTION, BLOCK, MINB>;
   if (smem > 227 * 1024) {
     set_error("hmc: %zu bytes of shared memory needed (D=%d, L=%d) exceed 227 KB", smem, n, l.p.num_steps);
     return MCMC_ENOTSUP;
@@ -328,8 +424,47 @@ int launch_hmc_variant(const Launch& l) {
   if (int rc = cuda_fail(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                          "cudaFuncSetAttribute(hmc)"))
     return rc;
-  const int64_t grid = (l.p.n_chains + BLOCK - 1) / BLOCK;
-  if (grid == 0) return MCMC_OK;
+  const int64_t groups = (l.p.n_chains + BLOCK - 1) / BLOCK;
+  if (groups == 0) return MCMC_OK;
+  a.n_groups = (int)groups;
+  a.n_chunks = 1;
+  a.chunk_iters = (int)(l.p.burn_in + l.p.num_samples);
+  a.queue = nullptr; a.flags = nullptr; a.ho_q = a.ho_g = a.ho_lp = nullptr; a.ho_acc = nullptr;
+  int64_t grid = groups;
+  // more groups than resident slots -> cut the run into chunks and balance them over persistent blocks
+  int per_sm = 0;
+  if (int rc = cuda_fail(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, BLOCK, smem), "occupancy(hmc)"))
+    return rc;
+  const int64_t slots = (int64_t)per_sm * device_sm_count();
+  const int64_t iters = l.p.burn_in + l.p.num_samples;
+  const size_t need = hmc_workspace_bytes(l.p);
+  const bool tuning_off = getenv("MCMC_HMC_NO_QUEUE") != nullptr;
+  const char* force = getenv("MCMC_HMC_FORCE_CHUNKS");  // test hook: chunk even when one wave would do
+  if (!tuning_off && slots > 0 && (groups > slots || force) && iters >= 2 && l.b.workspace &&
+      l.b.workspace_bytes >= need) {
+    int64_t nc = (12 * slots + groups - 1) / groups;   // about a dozen rounds of items per slot
+    if (force) nc = atoi(force);
+    if (nc < 2) nc = 2;
+    if (nc > iters) nc = iters;
+    const int64_t ci = (iters + nc - 1) / nc;
+    nc = (iters + ci - 1) / ci;
+    if (nc > 1) {
+      a.n_chunks = (int)nc;
+      a.chunk_iters = (int)ci;
+      char* w = reinterpret_cast<char*>(l.b.workspace);
+      const size_t C = (size_t)l.p.n_chains, D = (size_t)n;
+      const size_t flag_bytes = (((C + 31) / 32) * 4 + 255) / 256 * 256;
+      a.queue = reinterpret_cast<unsigned int*>(w);
+      a.flags = reinterpret_cast<unsigned int*>(w + 256);
+      a.ho_q = reinterpret_cast<double*>(w + 256 + flag_bytes);
+      a.ho_g = a.ho_q + C * D;
+      a.ho_lp = a.ho_g + C * D;
+      a.ho_acc = reinterpret_cast<int*>(a.ho_lp + C);
+      if (int rc = cuda_fail(cudaMemsetAsync(w, 0, 256 + flag_bytes, l.stream), "memset(hmc queue)")) return rc;
+      grid = slots < groups ? slots : groups;
+      if (force && grid > 1) grid = (grid + 1) / 2;  // fewer blocks than groups: items really migrate
+    }
+  }
   kern<<<(unsigned)grid, BLOCK, smem, l.stream>>>(a);
   return cuda_fail(cudaGetLastError(), "hmc_kernel launch");
 }

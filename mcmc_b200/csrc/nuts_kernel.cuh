@@ -52,13 +52,14 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
   extern __shared__ __align__(16) double smem[];
   double* sm_w = smem;
   double* sm_sqw = smem + n;
-  double* sm_tab = smem + 2 * n;
+  double* sm_logtab = smem + 2 * n;
+  double* sm_tab = sm_logtab + kRngTableDoubles;
   const int tabn = target_table_len(TID, n);
   // slot(s, d) = slots[(s*n + d) * stride + lane]
   double* slots;
   size_t stride;
   if (kSlotsInSmem) {
-    slots = smem + ((2 * n + tabn + 1) / 2) * 2 + tid;
+    slots = smem + ((2 * n + kRngTableDoubles + tabn + 1) / 2) * 2 + tid;
     stride = BLOCK;
   } else {
     const size_t cpad = ((size_t)C + 63) / 64 * 64;  // see nuts_workspace_bytes()
@@ -73,6 +74,7 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
     sm_sqw[d] = sqrt(w);
   }
   target_table_fill<TID>(a.t, n, sm_tab);
+  rng_table_fill(sm_logtab);
   __syncthreads();
 
   RngCtx rng;
@@ -80,6 +82,7 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
     const uint64_t gid = (uint64_t)(a.p.chain_offset + chain);
     rng.k0 = a.p.seed[0]; rng.k1 = a.p.seed[1];
     rng.gid_lo = (uint32_t)gid; rng.gid_hi = (uint32_t)(gid >> 32);
+    rng.logtab = sm_logtab;
   }
 
   // working point of the subtree being integrated
@@ -172,8 +175,8 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
           SLOT(SL_PL, d) = ps[d]; SLOT(SL_PR, d) = ps[d];
         }
         h0 = -lpp + 0.5 * kin;
-        const double u = injected ? a.b.u_inject[(size_t)it * C + chain] : philox_accept_uniform(rng, (uint32_t)it);
-        log_u = log(u) - h0;
+        const double lgu = injected ? log(a.b.u_inject[(size_t)it * C + chain]) : philox_accept_log_uniform(rng, (uint32_t)it);
+        log_u = lgu - h0;
         n_valid = 1; n_steps = 0; sum_alpha = 0.0; depth = 0; diverged = false;
         in_transition = true;
       }
@@ -303,7 +306,7 @@ int launch_nuts_variant(const Launch& l) {
   a.t = make_target_ctx(l.p, l.b.cov_inv);
   const int n = l.p.n_dim;
   const int tabn = target_table_len(TID, n);
-  size_t smem_d = (size_t)((2 * n + tabn + 1) / 2) * 2;
+  size_t smem_d = (size_t)((2 * n + kRngTableDoubles + tabn + 1) / 2) * 2;
   if (DS > 0) smem_d += (size_t)SL_COUNT * n * BLOCK;
   const size_t smem = smem_d * sizeof(double);
   if (DS == 0) {

@@ -9,6 +9,7 @@
 //   key = seed[0..1];  ctr = { gid_lo, gid_hi, iteration, (tag << 24) | block }
 #pragma once
 #include "common.cuh"
+#include "fastmath.cuh"
 
 namespace mcmc {
 
@@ -44,13 +45,13 @@ __device__ __forceinline__ double unif_oc(uint32_t hi, uint32_t lo) {
   return (double)(long long)(u53(hi, lo) + 1ull) * kTwoM53;
 }
 
-// two N(0,1) draws from one Philox block (Box-Muller, fp64)
-__device__ __forceinline__ void normal_pair(const U4& o, double& z0, double& z1) {
-  const double u1 = unif_oc(o.x, o.y);
-  const double u2 = unif_co(o.z, o.w);
-  const double rad = sqrt(-2.0 * log(u1));
+// two N(0,1) draws from one Philox block (Box-Muller, fp64).  The log / sqrt / sincos are the
+// branch-free integer-argument versions of fastmath.cuh (<= 2 ulp from libm's).
+__device__ __forceinline__ void normal_pair(const U4& o, const double* __restrict__ logtab, double& z0, double& z1) {
+  const double lg = fast_log_u53(u53(o.x, o.y) + 1ull, logtab);   // log of a uniform in (0,1]
+  const double rad = fast_sqrt_pos(-2.0 * lg);
   double s, c;
-  sincospi(2.0 * u2, &s, &c);
+  fast_sincos_u53(u53(o.z, o.w), &s, &c);                          // angle 2*pi*u2, u2 in [0,1)
   z0 = rad * c;
   z1 = rad * s;
 }
@@ -58,16 +59,26 @@ __device__ __forceinline__ void normal_pair(const U4& o, double& z0, double& z1)
 struct RngCtx {
   uint32_t k0, k1;       // key
   uint32_t gid_lo, gid_hi;
+  const double* logtab;  // shared-memory copy of kLogTabRaw
 };
+
+// cooperative copy of the log table into shared memory (256 doubles); call before __syncthreads()
+__device__ __forceinline__ void rng_table_fill(double* sm_logtab) {
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) sm_logtab[i] = kLogTabRaw[i];
+}
+constexpr int kRngTableDoubles = 256;
 
 __device__ __forceinline__ void philox_normals_block(const RngCtx& r, uint32_t it, uint32_t block,
                                                      double& z0, double& z1) {
-  normal_pair(philox4x32_10(r.gid_lo, r.gid_hi, it, (kTagNormal << 24) | block, r.k0, r.k1), z0, z1);
+  normal_pair(philox4x32_10(r.gid_lo, r.gid_hi, it, (kTagNormal << 24) | block, r.k0, r.k1), r.logtab, z0, z1);
 }
 
-__device__ __forceinline__ double philox_accept_uniform(const RngCtx& r, uint32_t it) {
+// log of the accept / slice uniform u in [0,1)  (log 0 = -inf: always accepted, as in the reference)
+__device__ __forceinline__ double philox_accept_log_uniform(const RngCtx& r, uint32_t it) {
   const U4 o = philox4x32_10(r.gid_lo, r.gid_hi, it, (kTagAccept << 24), r.k0, r.k1);
-  return unif_co(o.x, o.y);
+  const uint64_t k = u53(o.x, o.y);
+  const double lg = fast_log_u53(k | (k == 0), r.logtab);
+  return k == 0 ? -INFINITY : lg;
 }
 
 __device__ __forceinline__ void philox_nuts_uniforms(const RngCtx& r, uint32_t it, uint32_t depth,

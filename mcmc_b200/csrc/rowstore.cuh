@@ -97,4 +97,21 @@ __device__ __forceinline__ void store_row(double* dst, const double* row, int n_
   }
 }
 
+// per-thread row load (shared or global), 16-byte loads when aligned
+template <int DS>
+__device__ __forceinline__ void load_row(double* row, const double* src, int n_rt) {
+  const int nn = DS > 0 ? DS : n_rt;
+  if ((nn & 1) == 0 && ((((size_t)src) & 15) == 0)) {
+#pragma unroll
+    for (int d = 0; d < nn; d += 2) {
+      const double2 v = *reinterpret_cast<const double2*>(src + d);
+      row[d] = v.x;
+      row[d + 1] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int d = 0; d < nn; ++d) row[d] = src[d];
+  }
+}
+
 }  // namespace mcmc

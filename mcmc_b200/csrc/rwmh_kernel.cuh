@@ -34,9 +34,11 @@ __global__ void __launch_bounds__(BLOCK) rwmh_kernel(const RwmhKArgs a) {
 
   extern __shared__ __align__(16) double smem[];
   const int tabn = target_table_len(TID, n);
-  double* sm_tab = smem;
-  double* sm_stage = smem + ((tabn + 1) / 2) * 2;
+  double* sm_logtab = smem;
+  double* sm_tab = smem + kRngTableDoubles;
+  double* sm_stage = sm_tab + ((tabn + 1) / 2) * 2;
   target_table_fill<TID>(a.t, n, sm_tab);
+  rng_table_fill(sm_logtab);
   __syncthreads();
 
   TileWriter<DS, BLOCK> tw;
@@ -47,6 +49,7 @@ __global__ void __launch_bounds__(BLOCK) rwmh_kernel(const RwmhKArgs a) {
     const uint64_t gid = (uint64_t)(a.p.chain_offset + chain);
     rng.k0 = a.p.seed[0]; rng.k1 = a.p.seed[1];
     rng.gid_lo = (uint32_t)gid; rng.gid_hi = (uint32_t)(gid >> 32);
+    rng.logtab = sm_logtab;
   }
 
   double q[N], qn[N];
@@ -77,8 +80,8 @@ __global__ void __launch_bounds__(BLOCK) rwmh_kernel(const RwmhKArgs a) {
     }
     const double lpn = target_eval<TID, DS, true, false>(a.t, n, qn, nullptr, sm_tab);  // RWMH.py:102
     const double log_ratio = lpn - lp;
-    const double u = injected ? a.b.u_inject[(size_t)it * C + chain] : philox_accept_uniform(rng, (uint32_t)it);
-    const bool accept = log(u) < min_nan(0.0, log_ratio);  // RWMH.py:105-107
+    const double log_u = injected ? log(a.b.u_inject[(size_t)it * C + chain]) : philox_accept_log_uniform(rng, (uint32_t)it);
+    const bool accept = log_u < min_nan(0.0, log_ratio);  // RWMH.py:105-107
     if (accept) {
 #pragma unroll
       for (int d = 0; d < n; ++d) q[d] = qn[d];
@@ -114,7 +117,7 @@ int launch_rwmh_variant(const Launch& l) {
   const int n = l.p.n_dim;
   const bool store = !(l.p.flags & MCMC_FLAG_NO_SAMPLES) && l.b.samples != nullptr;
   const int tabn = target_table_len(TID, n);
-  const size_t smem = ((size_t)((tabn + 1) / 2) * 2 + (store ? 2 * (size_t)n * BLOCK : 0)) * sizeof(double);
+  const size_t smem = ((size_t)kRngTableDoubles + (size_t)((tabn + 1) / 2) * 2 + (store ? 2 * (size_t)n * BLOCK : 0)) * sizeof(double);
   auto kern = rwmh_kernel<TID, DS, BLOCK>;
   if (smem > 227 * 1024) {
     set_error("rwmh: %zu bytes of shared memory needed exceed 227 KB", smem);

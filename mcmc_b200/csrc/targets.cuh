@@ -203,6 +203,7 @@ __device__ __forceinline__ double target_eval(const TargetCtx& t, const int n_rt
     const double a = t.c[0];
     const double a4 = 4.0 * a, am2 = -2.0 * a;
     double U = 0.0;
+#if MCMC_IS_FAITHFUL
     double carry = 0.0;  // -2a t_{i-1}, the contribution of term i-1 to g_i
 #pragma unroll
     for (int i = 0; i < n - 1; ++i) {
@@ -216,6 +217,25 @@ __device__ __forceinline__ double target_eval(const TargetCtx& t, const int n_rt
       }
     }
     if (WANT_G) g[n - 1] = (n > 1) ? (0.0 + carry) : 0.0;
+#else
+    // 5 DFMA-pipe ops per coupling term: t, 4a*x, 2-2x, fma, fma
+    double tprev = 0.0;
+#pragma unroll
+    for (int i = 0; i < n - 1; ++i) {
+      const double ti = fma(-q[i], q[i], q[i + 1]);
+      if (WANT_LP) {
+        const double om = 1.0 - q[i];
+        U = fma(om, om, U);
+        U = fma(a * ti, ti, U);
+      }
+      if (WANT_G) {
+        const double gi = fma(q[i] * a4, ti, fma(-2.0, q[i], 2.0));
+        g[i] = (i == 0) ? gi : fma(am2, tprev, gi);
+        tprev = ti;
+      }
+    }
+    if (WANT_G) g[n - 1] = (n > 1) ? am2 * tprev : 0.0;
+#endif
     if (WANT_LP) lp = -U;
   } else if (TID == MCMC_TARGET_GAUSSIAN_MIXTURE) {
     const double hs = t.c[0];

@@ -199,3 +199,32 @@ def test_native_philox_stream_matches_oracle_and_is_shard_invariant(gpu_lib, ora
         a = g.run(smp, pf, q0)
         b = oracle.run(smp, pf, q0)
         assert relerr(a["samples"], b["samples"]) <= 1e-8, smp
+
+
+@pytest.mark.parametrize("sampler,sched", [(_abi.SAMPLER_HMC, None), (_abi.SAMPLER_GRAHMC, "tanh")])
+def test_chunked_work_queue_is_bit_identical(gpu_lib, oracle, sampler, sched, monkeypatch):
+    """The wave-balanced scheduler (iteration chunks handed between blocks through HBM) must not change
+    a single bit: counters are keyed on (chain, absolute iteration), the state hand-off is exact."""
+    C_, D, S, B, L = 300, 20, 11, 3, 8
+    i = _inputs("neals_funnel", C_, D, S, B, seed=41)
+    fl = _abi.FLAG_TRACK_PROPOSALS | _abi.FLAG_ACCUM_WELFORD
+    mk = lambda mode: oracle.make_params(tid("neals_funnel"), [], C_, D, S, B, L, i["eps"], gamma=1.0, steepness=0.5,
+                                         schedule_id=_abi.SCHEDULE_IDS.get(sched, 0), rng_mode=mode, seed=(7, 9),
+                                         flags=fl)
+    wf = (np.zeros((C_, D)), np.zeros((C_, D)))
+    g = GpuBackend("fast")
+    for mode, kw in ((_abi.RNG_INJECTED, dict(z=i["z"], u=i["u"])), (_abi.RNG_PHILOX, {})):
+        monkeypatch.delenv("MCMC_HMC_FORCE_CHUNKS", raising=False)
+        ref = g.run(sampler, mk(mode), i["q0"], inv_mass=i["w"], welford=wf, **kw)
+        for nchunks in ("2", "5", "14"):
+            monkeypatch.setenv("MCMC_HMC_FORCE_CHUNKS", nchunks)
+            got = g.run(sampler, mk(mode), i["q0"], inv_mass=i["w"], welford=wf, **kw)
+            for k in ref:
+                assert np.array_equal(ref[k], got[k], equal_nan=True), (mode, nchunks, k)
+    monkeypatch.delenv("MCMC_HMC_FORCE_CHUNKS", raising=False)
+    o = oracle.run(sampler, mk(_abi.RNG_INJECTED), i["q0"], inv_mass=i["w"], z=i["z"], u=i["u"], welford=wf)
+    monkeypatch.setenv("MCMC_HMC_FORCE_CHUNKS", "4")
+    got = g.run(sampler, mk(_abi.RNG_INJECTED), i["q0"], inv_mass=i["w"], z=i["z"], u=i["u"], welford=wf)
+    for k in ("samples", "prop_q", "delta_h", "final_g", "welford_mean", "welford_m2"):
+        assert relerr(got[k], o[k]) <= 1e-10, k
+    assert np.array_equal(got["accept_count"], o["accept_count"])
