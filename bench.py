@@ -58,6 +58,9 @@ class ClockSampler(threading.Thread):
         self.index = index
         self.rows = []
         self._stop_evt = threading.Event()
+        self._armed = threading.Event()   # rows are kept only while armed (= during the timed region)
+        self.ready = threading.Event()    # NVML initialised: nvmlInit can hold driver locks for milliseconds and
+                                          # must not run concurrently with the first timed launches
 
     def run(self):
         try:
@@ -70,17 +73,24 @@ class ClockSampler(threading.Thread):
                     (R.nvmlClocksThrottleReasonHwThermalSlowdown, "hw_thermal_slowdown"),
                     (R.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_thermal_slowdown"),
                     (R.nvmlClocksThrottleReasonSwPowerCap, "sw_power_cap")]
+            pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+            self.ready.set()
             while not self._stop_evt.is_set():
-                sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
-                rs = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                self.rows.append([str(sm), str(mx)] + ["active" if rs & b else "not active" for b, _ in bits])
+                if self._armed.is_set():
+                    sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                    rs = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    self.rows.append([str(sm), str(mx)] + ["active" if rs & b else "not active" for b, _ in bits])
                 self._stop_evt.wait(0.01)
             return
         except Exception:
             pass
+        self.ready.set()
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         while not self._stop_evt.is_set():
+            if not self._armed.is_set():
+                self._stop_evt.wait(0.01)
+                continue
             try:
                 o = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
                                    capture_output=True, text=True, timeout=5).stdout.strip()
@@ -89,6 +99,9 @@ class ClockSampler(threading.Thread):
             except Exception:
                 pass
             self._stop_evt.wait(0.1)
+
+    def arm(self):
+        self._armed.set()
 
     def stop(self):
         self._stop_evt.set()
@@ -210,15 +223,18 @@ def run_gpu_arm(args) -> None:
         torch.cuda.synchronize(dev)
 
     peak = fp64_peak_tflops()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        sampler.ready.wait(timeout=30)
 
     # ---- device-resident loop (value)
     for i in range(args.warmup):
         for L in L_GRID:
             one_call(L, q0_dev, -1 - i)
     barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
-        sampler.start()
+        sampler.arm()
     evs = []
     acc_sum = 0.0
     t_start = torch.cuda.Event(enable_timing=True)

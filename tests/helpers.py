@@ -53,3 +53,63 @@ class GpuBackend:
         from mcmc_b200.hostrun import run_host
         kw.pop("store_samples", None)
         return run_host(sampler, p, init_q, variant=self.variant, **kw)
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU stand-ins for the device calls of the tuning code, built on the oracle.  They let the
+# host-side logic (dual averaging, windowed Welford warmup, chain sharding + gloo reductions)
+# run in the CPU test suite; the product modules themselves never import the oracle.
+
+def oracle_sample_batch(sampler, log_prob_fn, position, key, num_samples, *, step_size, num_steps=0,
+                        inv_mass_matrix=None, gamma=0.0, steepness=1.0, schedule_id=0, max_tree_depth=10,
+                        welford=None, welford_count=0.0, store_samples=False, track_proposals=False, chain_offset=0):
+    import torch
+    from mcmc_b200.benchmarks.targets import resolve_log_prob
+    from mcmc_b200.random import as_key
+    from oracle import oracle as O
+    tag = resolve_log_prob(log_prob_fn)
+    q0 = np.ascontiguousarray(position.numpy() if hasattr(position, "numpy") else position, dtype=np.float64)
+    Cn, D = q0.shape
+    flags = (_abi.FLAG_ACCUM_WELFORD if welford is not None else 0)
+    p = O.make_params(tag.target_id, tag.target_params, Cn, D, num_samples, 0, num_steps, step_size, gamma=gamma,
+                      steepness=steepness, schedule_id=schedule_id, rng_mode=_abi.RNG_PHILOX, seed=tuple(as_key(key)),
+                      chain_offset=chain_offset, flags=flags, max_tree_depth=max_tree_depth)
+    w = None if welford is None else (welford[0].numpy(), welford[1].numpy())
+    im = None if inv_mass_matrix is None else np.asarray(inv_mass_matrix, dtype=np.float64)
+    r = O.run(sampler, p, q0, inv_mass=im, cov_inv=tag.cov_inv, welford=w, welford_count=welford_count)
+    if welford is not None:   # the kernels update the caller's arrays in place
+        welford[0].copy_(torch.from_numpy(r["welford_mean"]))
+        welford[1].copy_(torch.from_numpy(r["welford_m2"]))
+    out = {k: torch.from_numpy(np.ascontiguousarray(v.astype(np.int64) if v.dtype == np.uint64 else v))
+           for k, v in r.items()}
+    if sampler == _abi.SAMPLER_NUTS:
+        out["accept_sum"] = out["mean_accept_probs"].sum()
+    else:
+        out["accept_sum"] = out["counters"][0].to(torch.float64)
+    out["accept_terms"] = Cn * int(num_samples)
+    return out
+
+
+def oracle_welford_sum_var(m2, count):
+    import torch
+    from oracle import oracle as O
+    return torch.from_numpy(O.welford_finalize(m2.numpy(), count))
+
+
+def patch_tuning_to_oracle(monkeypatch=None):
+    """Route the tuning modules' device calls to the oracle stand-ins (tests only)."""
+    import torch
+    import importlib
+    adaptation = importlib.import_module("mcmc_b200.tuning.adaptation")
+    dual_averaging = importlib.import_module("mcmc_b200.tuning.dual_averaging")
+    seq = importlib.import_module("mcmc_b200.tuning.sequential_tune_grahmc")
+    as_cpu = lambda x: torch.as_tensor(np.asarray(x), dtype=torch.float64).contiguous() if not isinstance(
+        x, torch.Tensor) else x.to(torch.float64).contiguous()
+    pairs = [(adaptation, "sample_batch", oracle_sample_batch), (adaptation, "welford_sum_var", oracle_welford_sum_var),
+             (adaptation, "_as_state_tensor", as_cpu), (dual_averaging, "sample_batch", oracle_sample_batch),
+             (seq, "sample_batch", oracle_sample_batch)]
+    for mod, name, fn in pairs:
+        if monkeypatch is not None:
+            monkeypatch.setattr(mod, name, fn)
+        else:
+            setattr(mod, name, fn)
