@@ -193,6 +193,25 @@ int mcmc_chain_moments(const double* samples, int64_t num_samples, int64_t n_cha
 int mcmc_sum_f64(const double* x, int64_t n, double* out, void* workspace, size_t workspace_bytes,
                  void* stream);
 
+/* ---- cross-chain convergence diagnostics (run_benchmarks.py:161-195: az.rhat, az.ess, az.summary; the
+   published ArviZ algorithm, see mcmc_b200/csrc/diag.cu).  Device pointers, asynchronous on `stream`.
+
+   mcmc_rank_normalize: ArviZ `_z_scale` of one variable.  `sorted_vals` = its n values in ascending
+   order, `perm` = the permutation that sorted them; out_z[perm[i]] = Phi^-1((r_i - 3/8)/(n + 1/4)) with
+   r_i the average 1-based rank of sorted_vals[i] over ties.
+
+   mcmc_split_chain_stats: one variable laid out y[s*stride_s + c*stride_c].  Every chain c contributes
+   two sequences of half_len draws: rows [0, half_len) and rows [second_half_row, second_half_row +
+   half_len).  Outputs: acov_sum[t] = sum over the 2*n_chains sequences of the biased autocovariance at
+   lag t (t < n_lags <= half_len); mean_stats[0..2] = (count, mean, M2) of the sequence means.  R-hat and
+   ESS follow from these on the host (Geyer truncation) after the sums have been all-reduced over the
+   chain shards of a multi-GPU run.  Results are deterministic (fixed-order reductions). */
+int mcmc_rank_normalize(const double* sorted_vals, const int64_t* perm, int64_t n, double* out_z, void* stream);
+int mcmc_split_chain_stats_workspace(int64_t half_len, int64_t n_chains, int32_t n_lags, size_t* bytes);
+int mcmc_split_chain_stats(const double* y, int64_t half_len, int64_t second_half_row, int64_t n_chains,
+                           int64_t stride_s, int64_t stride_c, int32_t n_lags, double* acov_sum,
+                           double* mean_stats, void* workspace, size_t workspace_bytes, void* stream);
+
 /* register-resident DFMA throughput probe used as the fp64 roofline denominator:
    runs `iters` dependent-chain FMA rounds on every SM and returns flop count and ms */
 int mcmc_fp64_peak_probe(int iters, double* flops_out, float* ms_out, void* stream);

@@ -227,3 +227,59 @@ def get_target(name: str, dim: int = 10, **kwargs) -> TargetDistribution:
 
 def list_targets():
     return [f(10) for f in _FACTORIES.values()]
+
+
+# ---------------------------------------------------------------------------------------------
+# ground-truth samplers (targets.py:561-701) — host-side draws from the Philox stream
+
+def get_reference_sampler(target_name: str, dim: int = 10, **kwargs):
+    """(key, n) -> (n, dim) ground-truth draws, or None (targets.py:561-686).  Rosenbrock: the reference
+    loads benchmarks/reference_samples/rosenbrock_{20,50}d.npy, which are absent from its tree
+     -> None, as the reference itself returns when the file is missing."""
+    from ..random import bernoulli, gamma, normal, split
+    if target_name == "standard_normal":
+        return lambda key, n: normal(key, (n, dim))
+    if target_name == "correlated_gaussian":
+        rho = kwargs.get("correlation", 0.9)
+        Lc = np.linalg.cholesky((1.0 - rho) * np.eye(dim) + rho * np.ones((dim, dim)))
+        return lambda key, n: normal(key, (n, dim)) @ Lc.T
+    if target_name == "ill_conditioned_gaussian":
+        scales = np.sqrt(np.linspace(1.0, kwargs.get("condition_number", 100.0), dim))
+        return lambda key, n: normal(key, (n, dim)) * scales
+    if target_name == "student_t":
+        df = kwargs.get("df", 3.0)
+
+        def sampler(key, n):
+            k1, k2 = split(key)
+            z = normal(k1, (n, dim))
+            chi2 = gamma(k2, df / 2.0, (n, 1)) * 2.0
+            return z / np.sqrt(chi2 / df)
+        return sampler
+    if target_name == "log_gamma":
+        shape, rate = kwargs.get("shape", 2.0), kwargs.get("rate", 1.0)
+        return lambda key, n: gamma(key, shape, (n, dim)) / rate
+    if target_name == "neals_funnel":
+        def sampler(key, n):
+            k1, k2 = split(key)
+            v = normal(k1, (n,)) * 3.0
+            rest = normal(k2, (n, dim - 1)) * np.exp(v / 2.0)[:, None]
+            return np.concatenate([v[:, None], rest], axis=1)
+        return sampler
+    if target_name == "gaussian_mixture":
+        if kwargs.get("n_modes", 2) != 2:
+            return None
+        sep = kwargs.get("separation", 5.0)
+
+        def sampler(key, n):
+            k1, k2, k3 = split(key, 3)
+            comp = bernoulli(k1, 0.5, (n,))
+            x0 = normal(k2, (n,)) + np.where(comp, sep / 2.0, -sep / 2.0)
+            return np.concatenate([x0[:, None], normal(k3, (n, dim - 1))], axis=1)
+        return sampler
+    return None
+
+
+def has_reference_sampler(target_name: str) -> bool:
+    """targets.py:689-701."""
+    return target_name in ("standard_normal", "correlated_gaussian", "ill_conditioned_gaussian", "student_t",
+                           "log_gamma", "neals_funnel", "gaussian_mixture", "rosenbrock")

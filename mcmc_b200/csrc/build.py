@@ -27,6 +27,7 @@ HEADERS = ["common.cuh", "philox.cuh", "targets.cuh", "rowstore.cuh", "hmc_kerne
 
 def _units():
     yield "abi.cu", None
+    yield "diag.cu", None
     for fam in ("hmc_inst.cu", "rwmh_inst.cu", "nuts_inst.cu"):
         for t in range(NUM_TARGETS):
             yield fam, t

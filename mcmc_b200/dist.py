@@ -112,3 +112,33 @@ def gather_chains(x: torch.Tensor, dim: int = 0, max_per_rank: int | None = None
     outs = [torch.empty_like(x) for _ in range(world_size())]
     td.all_gather(outs, x)
     return torch.cat([o.narrow(dim, 0, k) for o, k in zip(outs, ns)], dim=dim)
+
+
+def variable_shard(n_dim: int, r: int | None = None, w: int | None = None) -> Tuple[int, int]:
+    """(first variable, count) owned by rank r when the D variables are dealt in contiguous blocks."""
+    w = world_size() if w is None else w
+    r = rank() if r is None else r
+    base, rem = divmod(int(n_dim), w)
+    return r * base + min(r, rem), base + (1 if r < rem else 0)
+
+
+def chains_to_variables(samples: torch.Tensor):
+    """Re-shard (S, C_local, D) from chains to variables: returns ((S, C_total, d_local), [variable ids]).
+    One all-to-all over NVLink (NCCL); gloo has no all-to-all, so the CPU test path all-gathers instead.
+    Every rank must hold the same number of chains."""
+    S, Cl, D = samples.shape
+    w, r = world_size(), rank()
+    d0, dn = variable_shard(D)
+    if w == 1:
+        return samples, list(range(D))
+    if td.get_backend() == "nccl":
+        # send block j = my chains of rank j's variables, (S, Cl, dn_j) contiguous
+        send = [samples[:, :, variable_shard(D, j, w)[0]:sum(variable_shard(D, j, w))].contiguous() for j in range(w)]
+        recv = [torch.empty((S, Cl, dn), dtype=samples.dtype, device=samples.device) for _ in range(w)]
+        td.all_to_all(recv, send)
+    else:
+        mine = samples.contiguous()
+        full = [torch.empty_like(mine) for _ in range(w)]
+        td.all_gather(full, mine)
+        recv = [f[:, :, d0:d0 + dn] for f in full]
+    return torch.cat(recv, dim=1), list(range(d0, d0 + dn))
