@@ -110,6 +110,8 @@ def lib(variant: str | None = None) -> C.CDLL:
     if variant in _LIBS:
         return _LIBS[variant]
     path = LIB_PATHS[variant]
+    if variant == "fast" and os.environ.get("MCMC_B200_LIB"):   # kernel experiments: an alternative build of the same ABI
+        path = os.environ["MCMC_B200_LIB"]
     if not os.path.exists(path):
         raise ImportError(
             f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "

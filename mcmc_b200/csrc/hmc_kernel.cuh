@@ -18,7 +18,15 @@
 #include "rowstore.cuh"
 #include "targets.cuh"
 
+// leapfrog steps per trip of the trajectory loop: with several steps in one basic block ptxas overlaps the
+// serial tail of one step's gradient with the drift of the next (2 warps per scheduler cannot hide it)
+#ifndef MCMC_STEP_UNROLL
+#define MCMC_STEP_UNROLL 4
+#endif
+
 namespace mcmc {
+
+constexpr int kStepUnroll = MCMC_STEP_UNROLL;
 
 struct HmcKArgs {
   McmcParams p;
@@ -186,24 +194,28 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
   lp = target_eval<TID, DS, true, true>(a.t, n, q, g, sm_tab);
   acc = 0;
   } else {
-    // ---- resume: wait for the previous chunk of this group, then fetch its state from HBM (L2)
+    // ---- resume: wait for the previous chunk of this group, then copy its state tiles from HBM (L2) straight
+    // into shared memory: the hand-off arrays hold the block's sm_q / sm_g tiles verbatim, so the copy is flat
+    // and fully coalesced
     if (tid == 0) {
       while (ld_acquire_u32(a.flags + grp) < (unsigned int)chunk) __nanosleep(200);
     }
     __syncthreads();
-    const double* sq = a.ho_q + chain * n;
-    const double* sg = a.ho_g + chain * n;
-#pragma unroll
-    for (int d = 0; d < n; ++d) {
-      q[d] = __ldcg(sq + d);
-      g[d] = __ldcg(sg + d);
+    const double* sq = a.ho_q + (size_t)chain0 * n;
+    const double* sg = a.ho_g + (size_t)chain0 * n;
+    for (int k = tid; k < BLOCK * n; k += BLOCK) {
+      sm_q[k] = __ldcg(sq + k);
+      sm_g[k] = __ldcg(sg + k);
     }
-    lp = __ldcg(a.ho_lp + chain);
-    acc = __ldcg(a.ho_acc + chain);
+    lp = __ldcg(a.ho_lp + chain0 + tid);
+    acc = __ldcg(a.ho_acc + chain0 + tid);
+    __syncthreads();
   }
-  store_row<DS>(my_q, q, n);
+  if (chunk == 0) {
+    store_row<DS>(my_q, q, n);
 #pragma unroll
-  for (int d = 0; d < n; ++d) sm_g[d * BLOCK + tid] = g[d];
+    for (int d = 0; d < n; ++d) sm_g[d * BLOCK + tid] = g[d];
+  }
   double wcount = a.b.welford_count + (double)((it_begin > B) ? (it_begin - B) : 0);
 
   for (int64_t it = it_begin; it < it_end; ++it) {
@@ -269,6 +281,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
 #pragma unroll
         for (int d = 0; d < n; ++d) p[d] = fma(half_eps, g[d], p[d]);
       }
+#pragma unroll kStepUnroll
       for (int i = 0; i < L - 1; ++i) {
 #pragma unroll
         for (int d = 0; d < n; ++d) q[d] = fma(p[d], sm_epsw[d], q[d]);
@@ -362,28 +375,26 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
     }
   }
   if (bulk && tid == 0) bulk_wait_all();
-  load_row<DS>(q, my_q, n);
-#pragma unroll
-  for (int d = 0; d < n; ++d) g[d] = sm_g[d * BLOCK + tid];
 
   if (!last_chunk) {
-    // ---- hand the group's state to whoever takes its next chunk
-    if (active) {
-      double* dq = a.ho_q + chain * n;
-      double* dg = a.ho_g + chain * n;
-#pragma unroll
-      for (int d = 0; d < n; ++d) {
-        __stcg(dq + d, q[d]);
-        __stcg(dg + d, g[d]);
-      }
-      __stcg(a.ho_lp + chain, lp);
-      __stcg(a.ho_acc + chain, acc);
+    // ---- hand the group's state tiles to whoever takes its next chunk (flat coalesced copy of sm_q / sm_g)
+    __syncthreads();
+    double* dq = a.ho_q + (size_t)chain0 * n;
+    double* dg = a.ho_g + (size_t)chain0 * n;
+    for (int k = tid; k < BLOCK * n; k += BLOCK) {
+      __stcg(dq + k, sm_q[k]);
+      __stcg(dg + k, sm_g[k]);
     }
+    __stcg(a.ho_lp + chain0 + tid, lp);
+    __stcg(a.ho_acc + chain0 + tid, acc);
     __threadfence();
     __syncthreads();
     if (tid == 0) st_release_u32(a.flags + grp, (unsigned int)chunk + 1u);
   } else {
   // ---- epilogue: final state, acceptance statistics
+  load_row<DS>(q, my_q, n);
+#pragma unroll
+  for (int d = 0; d < n; ++d) g[d] = sm_g[d * BLOCK + tid];
   if (active) {
     if (a.b.accept_count) a.b.accept_count[chain] = acc;
     if (a.b.accept_rate) a.b.accept_rate[chain] = (float)acc / (float)S;  // HMC.py:313
@@ -442,17 +453,23 @@ int launch_hmc_variant(const Launch& l) {
   const char* force = getenv("MCMC_HMC_FORCE_CHUNKS");  // test hook: chunk even when one wave would do
   if (!tuning_off && slots > 0 && (groups > slots || force) && iters >= 2 && l.b.workspace &&
       l.b.workspace_bytes >= need) {
-    int64_t nc = (12 * slots + groups - 1) / groups;   // about a dozen rounds of items per slot
-    if (force) nc = atoi(force);
-    if (nc < 2) nc = 2;
-    if (nc > iters) nc = iters;
-    const int64_t ci = (iters + nc - 1) / nc;
+    // chunk length: an item should cost about kItemCost leapfrog-step equivalents (an iteration costs L steps
+    // + ~14 for the momentum draw / MH test): short enough that the last wave of items is a small tail, long
+    // enough that the hand-off through L2 stays in the noise; and never fewer than ~6 items per slot
+    const char* cost_env = getenv("MCMC_HMC_ITEM_COST");  // tuning knob (experiments only)
+    const int64_t item_cost = cost_env ? atoi(cost_env) : 450;
+    int64_t ci = item_cost / (l.p.num_steps + 14);
+    const int64_t ci_bal = iters * groups / (6 * slots);
+    if (ci > ci_bal) ci = ci_bal;
+    if (ci < 1) ci = 1;
+    int64_t nc = (iters + ci - 1) / ci;
+    if (force) { nc = atoi(force); if (nc < 2) nc = 2; if (nc > iters) nc = iters; ci = (iters + nc - 1) / nc; }
     nc = (iters + ci - 1) / ci;
     if (nc > 1) {
       a.n_chunks = (int)nc;
       a.chunk_iters = (int)ci;
       char* w = reinterpret_cast<char*>(l.b.workspace);
-      const size_t C = (size_t)l.p.n_chains, D = (size_t)n;
+      const size_t C = ((size_t)l.p.n_chains + 63) / 64 * 64, D = (size_t)n;   // whole tiles, also for the tail group
       const size_t flag_bytes = (((C + 31) / 32) * 4 + 255) / 256 * 256;
       a.queue = reinterpret_cast<unsigned int*>(w);
       a.flags = reinterpret_cast<unsigned int*>(w + 256);
