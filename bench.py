@@ -41,7 +41,7 @@ STEP_SIZE = 0.02         # fixed epsilon, see DESIGN.md (short dual-averaging ru
 INV_MASS = np.linspace(0.5, 2.0, D)  # a non-trivial diagonal M^-1 to exercise the path
 SEED = (0, 0)
 # algorithmic fp64 flops of THIS kernel's formulation (FMA = 2), DESIGN.md "flop model"
-F_STEP = 251.0           # per leapfrog step of one 20-D rosenbrock chain: 80 integrator + 171 gradient
+F_STEP = 231.0           # per leapfrog step of one 20-D rosenbrock chain: 80 integrator (2 DFMA/dim) + 151 gradient (75 DFMA + 1 DMUL)
 F_ITER = 190.0           # per MH iteration outside the trajectory (momentum scaling, two kinetic energies, value)
 
 

@@ -218,7 +218,8 @@ __device__ __forceinline__ double target_eval(const TargetCtx& t, const int n_rt
     }
     if (WANT_G) g[n - 1] = (n > 1) ? (0.0 + carry) : 0.0;
 #else
-    // 5 DFMA-pipe ops per coupling term: t, 4a*x, 2-2x, fma, fma
+    // 4 DFMA per coupling term: with t_i = x_{i+1} - x_i^2,
+    //   g_i = 2(1 - x_i) + 4a x_i t_i - 2a t_{i-1} = x_i (4a t_i - 2) + 2 - 2a t_{i-1}
     double tprev = 0.0;
 #pragma unroll
     for (int i = 0; i < n - 1; ++i) {
@@ -229,8 +230,8 @@ __device__ __forceinline__ double target_eval(const TargetCtx& t, const int n_rt
         U = fma(a * ti, ti, U);
       }
       if (WANT_G) {
-        const double gi = fma(q[i] * a4, ti, fma(-2.0, q[i], 2.0));
-        g[i] = (i == 0) ? gi : fma(am2, tprev, gi);
+        const double hi = fma(q[i], fma(a4, ti, -2.0), 2.0);
+        g[i] = (i == 0) ? hi : fma(am2, tprev, hi);
         tprev = ti;
       }
     }
