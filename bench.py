@@ -56,6 +56,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, index: int):
         super().__init__(daemon=True)
         self.index = index
+        self.period = float(os.environ.get("MCMC_BENCH_CLOCK_PERIOD", "0.01"))
         self.rows = []
         self._stop_evt = threading.Event()
         self._armed = threading.Event()   # rows are kept only while armed (= during the timed region)
@@ -80,7 +81,7 @@ class ClockSampler(threading.Thread):
                     sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
                     rs = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
                     self.rows.append([str(sm), str(mx)] + ["active" if rs & b else "not active" for b, _ in bits])
-                self._stop_evt.wait(0.01)
+                self._stop_evt.wait(self.period)
             return
         except Exception:
             pass
@@ -201,6 +202,7 @@ def run_gpu_arm(args) -> None:
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=dev)
     _abi.check(_abi.lib("fast").mcmc_set_device(local))
 
@@ -229,13 +231,18 @@ def run_gpu_arm(args) -> None:
         sampler.ready.wait(timeout=30)
 
     # ---- device-resident loop (value)
+    out = None
     for i in range(args.warmup):
         for L in L_GRID:
-            one_call(L, q0_dev, -1 - i)
+            # keep the previous result alive while the next call allocates, exactly like the timed loop: torch's
+            # caching allocator then owns BOTH 705 MB sample blocks before timing starts (a cudaMalloc inside the
+            # timed region stalls the stream for milliseconds)
+            out = one_call(L, q0_dev, -1 - i)
     barrier()
     if sampler:
         sampler.arm()
     evs = []
+    host_ms = {}
     acc_sum = 0.0
     t_start = torch.cuda.Event(enable_timing=True)
     t_end = torch.cuda.Event(enable_timing=True)
@@ -244,12 +251,16 @@ def run_gpu_arm(args) -> None:
         for L in L_GRID:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
+            h0 = time.perf_counter()
             out = one_call(L, q0_dev, i)
+            host_ms[L] = host_ms.get(L, 0.0) + 1e3 * (time.perf_counter() - h0)
             e1.record()
             evs.append((L, e0, e1))
     t_end.record()
     barrier()
     dev_ms = t_start.elapsed_time(t_end)
+    if os.environ.get("MCMC_BENCH_DEBUG"):
+        print("host ms per call:", {L: round(v / args.steps, 3) for L, v in host_ms.items()}, file=sys.stderr)
     clocks = sampler.stop() if sampler else None
     acc_sum = float(out[2].mean().item())
     kern_ms = {L: 0.0 for L in L_GRID}
