@@ -4,12 +4,14 @@
 // the fp64 peak probe.  No exception crosses this file; no CPU compute path exists.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
 
 #include "common.cuh"
 #include "hmc_kernel.cuh"
+#include "philox.cuh"
 
 namespace mcmc {
 
@@ -22,11 +24,34 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-size_t nuts_workspace_bytes(const McmcParams& p) {
-  if (p.n_dim == 20 || p.n_dim == 10) return 0;  // tree ends live in shared memory
-  const size_t cpad = ((size_t)p.n_chains + 63) / 64 * 64;
-  return (size_t)8 * p.n_dim * cpad * sizeof(double);
+NutsWs nuts_ws_layout(const McmcParams& p) {
+  NutsWs w{};
+  const size_t C = (size_t)p.n_chains, D = (size_t)p.n_dim;
+  w.cpad = (C + 63) / 64 * 64;
+  auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+  size_t off = 0;
+  w.slots_off = off; off += up((size_t)8 * D * w.cpad * sizeof(double));
+  w.lp_off = off;    off += up(w.cpad * sizeof(double));
+  w.acc_off = off;   off += up(w.cpad * sizeof(int));
+  const int64_t T = p.burn_in + p.num_samples;
+  w.tseg = T > 0 ? T : 1;
+  w.z_off = w.lu_off = off;
+  if (p.rng_mode == MCMC_RNG_PHILOX && C > 0 && T > 0) {
+    // draw buffer capped (default 4 GiB; MCMC_NUTS_RNG_CAP_MB is a test hook that forces segmentation)
+    size_t cap = (size_t)4 << 30;
+    if (const char* e = getenv("MCMC_NUTS_RNG_CAP_MB")) cap = (size_t)atoll(e) << 20;
+    const size_t per_it = C * (D + 1) * sizeof(double);
+    int64_t ts = (int64_t)(cap / per_it);
+    if (ts < 1) ts = 1;
+    if (ts < T) w.tseg = ts;
+    w.z_off = off;  off += up((size_t)w.tseg * C * D * sizeof(double));
+    w.lu_off = off; off += up((size_t)w.tseg * C * sizeof(double));
+  }
+  w.total = off + 256;
+  return w;
 }
+
+size_t nuts_workspace_bytes(const McmcParams& p) { return nuts_ws_layout(p).total; }
 
 size_t hmc_workspace_bytes(const McmcParams& p) {
   // queue + flags + hand-off state (q, g, lp, acc) of the chunked scheduler in hmc_kernel.cuh
@@ -212,6 +237,50 @@ __global__ void __launch_bounds__(256) fp64_probe_kernel(int iters, double* sink
   }
   const double s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
   if (s == 123.456) sink[0] = s;
+}
+
+// ------------------------------------------------------------------ native draws for NUTS (see nuts_kernel.cuh)
+
+// one thread per (iteration, chain): 20 normals (10 Philox blocks) + the log of the accept uniform, with the
+// counters of philox.cuh -> identical values to an in-kernel draw; rows leave as 16-byte stores
+__global__ void __launch_bounds__(128) nuts_rng_fill_kernel(McmcParams p, int64_t it_begin, int64_t n_it,
+                                                            double* __restrict__ z, double* __restrict__ logu) {
+  __shared__ double sm_logtab[kRngTableDoubles];
+  rng_table_fill(sm_logtab);
+  __syncthreads();
+  const int64_t C = p.n_chains;
+  const int n = p.n_dim;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_it * C) return;
+  const int64_t t = idx / C, c = idx - t * C;
+  RngCtx rng;
+  const uint64_t gid = (uint64_t)(p.chain_offset + c);
+  rng.k0 = p.seed[0]; rng.k1 = p.seed[1];
+  rng.gid_lo = (uint32_t)gid; rng.gid_hi = (uint32_t)(gid >> 32);
+  rng.logtab = sm_logtab;
+  const uint32_t it = (uint32_t)(it_begin + t);
+  double* row = z + (size_t)idx * n;
+  const bool vec = ((n & 1) == 0);
+  for (int j = 0; 2 * j < n; ++j) {
+    double z0, z1;
+    philox_normals_block(rng, it, (uint32_t)j, z0, z1);
+    if (vec) {
+      *reinterpret_cast<double2*>(row + 2 * j) = make_double2(z0, z1);
+    } else {
+      row[2 * j] = z0;
+      if (2 * j + 1 < n) row[2 * j + 1] = z1;
+    }
+  }
+  logu[idx] = philox_accept_log_uniform(rng, it);
+}
+
+int launch_rng_fill(const McmcParams& p, int64_t it_begin, int64_t it_end, double* z, double* logu, cudaStream_t s) {
+  const int64_t total = (it_end - it_begin) * p.n_chains;
+  if (total <= 0) return MCMC_OK;
+  const int64_t grid = (total + 127) / 128;
+  if (grid > 0x7fffffffLL) { set_error("nuts rng fill: segment too large"); return MCMC_ENOTSUP; }
+  nuts_rng_fill_kernel<<<(unsigned)grid, 128, 0, s>>>(p, it_begin, it_end - it_begin, z, logu);
+  return cuda_fail(cudaGetLastError(), "nuts_rng_fill launch");
 }
 
 // ------------------------------------------------------------------ host arena (mcmc_run_host)

@@ -59,7 +59,16 @@ template <int TID> int launch_target_eval(const McmcParams& p, const double* cov
                                           int64_t n, double* lp, double* grad, cudaStream_t s);
 
 // workspace layouts (bytes), shared by the launchers and mcmc_workspace_bytes
+struct NutsWs {
+  size_t cpad;       // chains padded to whole warps of 64
+  size_t slots_off, lp_off, acc_off, z_off, lu_off, total;
+  int64_t tseg;      // iterations per segment of the native draw buffer
+};
+NutsWs nuts_ws_layout(const McmcParams& p);
 size_t nuts_workspace_bytes(const McmcParams& p);
+// z[(it - it_begin)*C*D + c*D + d], logu[(it - it_begin)*C + c] for it in [it_begin, it_end): the momentum normals and
+// the log of the slice / accept uniform of the native Philox stream (counter layout of philox.cuh)
+int launch_rng_fill(const McmcParams& p, int64_t it_begin, int64_t it_end, double* z, double* logu, cudaStream_t s);
 size_t hmc_workspace_bytes(const McmcParams& p);
 int device_sm_count();
 

@@ -228,3 +228,28 @@ def test_chunked_work_queue_is_bit_identical(gpu_lib, oracle, sampler, sched, mo
     for k in ("samples", "prop_q", "delta_h", "final_g", "welford_mean", "welford_m2"):
         assert relerr(got[k], o[k]) <= 1e-10, k
     assert np.array_equal(got["accept_count"], o["accept_count"])
+
+
+def test_nuts_native_stream_segments_are_bit_identical(gpu_lib, oracle, monkeypatch):
+    """NUTS draws its momenta with a separate convergent kernel into a bounded buffer; a run longer than the buffer is
+    cut into segments of iterations whose state travels through the workspace.  Neither must change a bit, and the
+    stream equals the oracle's in-loop Philox draws."""
+    C_, D, S, B = 70, 20, 9, 3
+    q0 = np.random.default_rng(8).standard_normal((C_, D))
+    wf = (np.zeros((C_, D)), np.zeros((C_, D)))
+    p = oracle.make_params(tid("neals_funnel"), [], C_, D, S, B, 0, 0.15, rng_mode=_abi.RNG_PHILOX, seed=(5, 6),
+                           max_tree_depth=6, flags=_abi.FLAG_ACCUM_WELFORD)
+    g = GpuBackend("fast")
+    monkeypatch.delenv("MCMC_NUTS_RNG_CAP_MB", raising=False)
+    ref = g.run(_abi.SAMPLER_NUTS, p, q0, welford=wf)
+    o = oracle.run(_abi.SAMPLER_NUTS, p, q0, welford=wf)
+    assert np.array_equal(ref["tree_depths"], o["tree_depths"])
+    for k in ("samples", "log_probs", "mean_accept_probs", "final_q", "final_g", "welford_mean", "welford_m2"):
+        assert relerr(ref[k], o[k]) <= 1e-9, k
+    for j in range(4):
+        assert int(ref["counters"][j]) == int(o["counters"][j]), j
+    # 70 chains x 21 doubles = 11.8 KB per iteration: a "0 MB" cap gives one-iteration segments (12 launches)
+    monkeypatch.setenv("MCMC_NUTS_RNG_CAP_MB", "0")
+    seg = g.run(_abi.SAMPLER_NUTS, p, q0, welford=wf)
+    for k in ref:
+        assert np.array_equal(ref[k], seg[k], equal_nan=True), k
