@@ -160,15 +160,17 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
         in_subtree = false;
         // cond_fn (NUTS.py:243-248) on (q_right - q_left) . p_left / p_right; NaN compares false -> no U-turn
         const double* oth = wbase + (reg_dir > 0 ? SL_QL : SL_QR) * n * 32;
-        double dl = 0.0, dr = 0.0;
+        // with e = q_work - q_other:  working end on the right: (dl, dr) = (e.p_other, e.p_work);
+        // on the left q_right - q_left = -e: (dl, dr) = (-(e.p_work), -(e.p_other)) — negation commutes with
+        // every rounding, so this is the reference's value bit for bit
+        double eo = 0.0, ew = 0.0;
 #pragma unroll
         for (int d = 0; d < n; ++d) {
-          const double qo = oth[d * 32], po = oth[(n + d) * 32];
-          const double dq = reg_dir > 0 ? qs[d] - qo : qo - qs[d];
-          const double pl = reg_dir > 0 ? po : ps[d], pr = reg_dir > 0 ? ps[d] : po;
-          dl += dq * pl;
-          dr += dq * pr;
+          const double e = qs[d] - oth[d * 32];
+          eo += e * oth[(n + d) * 32];
+          ew += e * ps[d];
         }
+        const double dl = reg_dir > 0 ? eo : -ew, dr = reg_dir > 0 ? ew : -eo;
         u_turn = (dl < 0) | (dr < 0);
       }
       if (!in_transition) {
@@ -294,7 +296,7 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
         kin += (ps[d] * ps[d]) * sm_w[d];
       }
       h_new = -lps + 0.5 * kin;                   // NUTS.py:178 / :282
-      sa = sa + exp(min_nan(0.0, h0 - h_new));    // NUTS.py:179-181
+      sa = sa + exp_nonpos(min_nan(0.0, h0 - h_new));    // NUTS.py:179-181
       k -= 1;
     }
   }

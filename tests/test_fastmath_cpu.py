@@ -46,3 +46,38 @@ def test_fastmath_matches_libm(tmp_path):
     assert abs_near1 <= 3e-17      # log(u) for u within 1e-12 of 1
     assert rel_sq <= 2.3e-16       # <= 1 ulp
     assert abs_sc <= 3.4e-16
+
+
+SRC_EXP = r'''
+#include <cstdio>
+#include <cmath>
+#include <cstdint>
+#include <random>
+#include "%s/mcmc_b200/csrc/fastmath.cuh"
+using namespace mcmc;
+int main() {
+  std::mt19937_64 g(2);
+  std::uniform_real_distribution<double> U(0.0, 1.0);
+  double rel = 0;
+  for (long i = 0; i < 2000000; i++) {
+    double x = (i %% 3 == 0) ? -U(g) * 700.0 : ((i %% 3 == 1) ? -U(g) * 5.0 : -exp(-40.0 * U(g)));
+    if (i < 8) x = -0.25 * (double)i;
+    const double a = exp_nonpos(x);
+    const long double b = expl((long double)x);
+    rel = fmax(rel, (double)(fabsl((long double)a - b) / b));
+  }
+  const double z = exp_nonpos(0.0), tiny = exp_nonpos(-800.0), nn = exp_nonpos(NAN), mi = exp_nonpos(-INFINITY);
+  printf("%%.3e %%.17g %%.17g %%d %%.17g\n", rel, z, tiny, (int)(nn != nn), mi);
+  return 0;
+}
+'''
+
+
+def test_exp_nonpos_matches_libm(tmp_path):
+    src = tmp_path / "fe.cpp"
+    src.write_text(SRC_EXP % ROOT)
+    exe = tmp_path / "fe"
+    subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-ffp-contract=off", str(src), "-o", str(exe)])
+    rel, z, tiny, isnan, mi = subprocess.check_output([str(exe)]).split()
+    assert float(rel) <= 2.3e-16       # <= 1 ulp against long double
+    assert float(z) == 1.0 and float(tiny) == 0.0 and int(isnan) == 1 and float(mi) == 0.0

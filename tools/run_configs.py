@@ -138,7 +138,7 @@ def config5(chains_total, S):
              ("neals_funnel", T.neals_funnel(D), 0.1, lambda k: T.neals_funnel(D).init_sampler(k, C)))
     for name, tgt, eps, init in cases:
         q0 = torch.from_numpy(init(300 + dist.rank())).cuda()
-        nuts_run(1, tgt.log_prob_fn, q0, eps, 4, burn_in=0, _chain_offset=off)
+        nuts_run(1, tgt.log_prob_fn, q0, eps, S, burn_in=32, _chain_offset=off)   # same shapes: buffers come from torch's cache
         with Timer() as tm:
             smp, lps, acc, st, depths, maps = nuts_run(2, tgt.log_prob_fn, q0, eps, S, burn_in=32, _chain_offset=off)
         # grad-evals = sum 2^depth - 1 over transitions (run_benchmarks.py:724), counted over stored iterations here
