@@ -55,7 +55,7 @@ size_t nuts_workspace_bytes(const McmcParams& p) { return nuts_ws_layout(p).tota
 
 size_t hmc_workspace_bytes(const McmcParams& p) {
   // queue + flags + hand-off state (q, g, lp, acc) of the chunked scheduler in hmc_kernel.cuh
-  const size_t C = ((size_t)p.n_chains + 63) / 64 * 64, D = (size_t)p.n_dim;
+  const size_t C = ((size_t)p.n_chains + 255) / 256 * 256, D = (size_t)p.n_dim;
   const size_t flag_bytes = (((C + 31) / 32) * 4 + 255) / 256 * 256;
   return 256 + flag_bytes + (2 * C * D + C) * sizeof(double) + C * sizeof(int) + 256;
 }

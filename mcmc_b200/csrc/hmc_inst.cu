@@ -4,6 +4,7 @@
 #include <cstring>
 
 #include "hmc_kernel.cuh"
+#include "hmc_ws_kernel.cuh"
 
 #ifndef MCMC_TID
 #error "compile with -DMCMC_TID=<target id>"
@@ -29,6 +30,14 @@ int launch_hmc<MCMC_TID>(const Launch& l, bool friction) {
     }
   }
 #endif
+  // large batches under the native stream: the warp-specialised kernel (producer warps draw the momenta)
+  if (l.p.n_dim == 20 || l.p.n_dim == 10) {
+    bool used = false;
+    int rc;
+    if (l.p.n_dim == 20) rc = friction ? launch_hmc_ws<MCMC_TID, 20, true>(l, &used) : launch_hmc_ws<MCMC_TID, 20, false>(l, &used);
+    else rc = friction ? launch_hmc_ws<MCMC_TID, 10, true>(l, &used) : launch_hmc_ws<MCMC_TID, 10, false>(l, &used);
+    if (rc != MCMC_OK || used) return rc;
+  }
   switch (l.p.n_dim) {
     case 20:
       return friction ? launch_hmc_variant<MCMC_TID, 20, true, 64>(l) : launch_hmc_variant<MCMC_TID, 20, false, 64>(l);

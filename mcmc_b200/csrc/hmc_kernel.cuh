@@ -469,7 +469,7 @@ int launch_hmc_variant(const Launch& l) {
       a.n_chunks = (int)nc;
       a.chunk_iters = (int)ci;
       char* w = reinterpret_cast<char*>(l.b.workspace);
-      const size_t C = ((size_t)l.p.n_chains + 63) / 64 * 64, D = (size_t)n;   // whole tiles, also for the tail group
+      const size_t C = ((size_t)l.p.n_chains + 255) / 256 * 256, D = (size_t)n;   // whole tiles, also for the tail group
       const size_t flag_bytes = (((C + 31) / 32) * 4 + 255) / 256 * 256;
       a.queue = reinterpret_cast<unsigned int*>(w);
       a.flags = reinterpret_cast<unsigned int*>(w + 256);

@@ -253,3 +253,36 @@ def test_nuts_native_stream_segments_are_bit_identical(gpu_lib, oracle, monkeypa
     seg = g.run(_abi.SAMPLER_NUTS, p, q0, welford=wf)
     for k in ref:
         assert np.array_equal(ref[k], seg[k], equal_nan=True), k
+
+
+@pytest.mark.parametrize("name,sampler,sched,D", [("rosenbrock", _abi.SAMPLER_HMC, None, 20),
+                                                  ("neals_funnel", _abi.SAMPLER_GRAHMC, "tanh", 20),
+                                                  ("standard_normal", _abi.SAMPLER_GRAHMC, "constant", 10),
+                                                  ("student_t", _abi.SAMPLER_HMC, None, 10)])
+def test_warp_specialised_kernel_is_bit_identical(gpu_lib, oracle, monkeypatch, name, sampler, sched, D):
+    """hmc_ws_kernel (producer warps draw the momenta into a shared-memory ring, consumer warps integrate) against
+    hmc_kernel: same Philox counters, same arithmetic -> the same bits; with and without the chunked queue, with a
+    ragged tail (C not a multiple of 32), Welford accumulation and the no-samples mode."""
+    C_, S, B, L = 700, 7, 2, 5
+    i = _inputs(name, C_, D, S, B, seed=77)
+    g = GpuBackend("fast")
+    wf = (np.zeros((C_, D)), np.zeros((C_, D)))
+    for flags in (_abi.FLAG_ACCUM_WELFORD, _abi.FLAG_NO_SAMPLES | _abi.FLAG_ACCUM_WELFORD, 0):
+        p = oracle.make_params(tid(name), i["params"], C_, D, S, B, L, i["eps"], gamma=0.6, steepness=0.5,
+                               schedule_id=_abi.SCHEDULE_IDS.get(sched, 0), rng_mode=_abi.RNG_PHILOX, seed=(3, 4),
+                               chain_offset=1000, flags=flags)
+        kw = dict(inv_mass=i["w"])
+        if flags & _abi.FLAG_ACCUM_WELFORD:
+            kw["welford"] = wf
+        monkeypatch.setenv("MCMC_HMC_WS", "0")
+        monkeypatch.delenv("MCMC_HMC_FORCE_CHUNKS", raising=False)
+        ref = g.run(sampler, p, i["q0"], **kw)
+        monkeypatch.setenv("MCMC_HMC_WS", "1")
+        for nchunks in (None, "3", "9"):
+            if nchunks:
+                monkeypatch.setenv("MCMC_HMC_FORCE_CHUNKS", nchunks)
+            got = g.run(sampler, p, i["q0"], **kw)
+            for k in ref:
+                assert np.array_equal(ref[k], got[k], equal_nan=True), (flags, nchunks, k)
+    monkeypatch.delenv("MCMC_HMC_FORCE_CHUNKS", raising=False)
+    monkeypatch.delenv("MCMC_HMC_WS", raising=False)
