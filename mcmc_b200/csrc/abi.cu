@@ -27,12 +27,21 @@ void set_error(const char* fmt, ...) {
 NutsWs nuts_ws_layout(const McmcParams& p) {
   NutsWs w{};
   const size_t C = (size_t)p.n_chains, D = (size_t)p.n_dim;
-  w.cpad = (C + 63) / 64 * 64;
   auto up = [](size_t x) { return (x + 255) / 256 * 256; };
   size_t off = 0;
-  w.slots_off = off; off += up((size_t)8 * D * w.cpad * sizeof(double));
-  w.lp_off = off;    off += up(w.cpad * sizeof(double));
-  w.acc_off = off;   off += up(w.cpad * sizeof(int));
+  // lane tiles in global memory only for the runtime-D kernel (compiled D keeps them in shared memory);
+  // at most 8 resident warps per SM there, and never more warps than chains need
+  const bool smem_tiles = (p.n_dim == 10 || p.n_dim == 20);
+  int sms = device_sm_count();
+  if (sms <= 0) sms = 148;
+  w.max_warps = smem_tiles ? (int64_t)sms * 32 : (int64_t)sms * 8;
+  const int64_t need_warps = ((int64_t)C + 31) / 32;
+  const int64_t tile_warps = smem_tiles ? 0 : (need_warps < w.max_warps ? need_warps : w.max_warps);
+  w.slots_off = off; off += up((size_t)tile_warps * 5 * D * 32 * sizeof(double));
+  w.home_off = off;  off += up(C * 2 * D * sizeof(double));
+  w.lp_off = off;    off += up(C * sizeof(double));
+  w.acc_off = off;   off += up(C * sizeof(int));
+  w.queue_off = off; off += up((64 + C) * sizeof(unsigned int));
   const int64_t T = p.burn_in + p.num_samples;
   w.tseg = T > 0 ? T : 1;
   w.z_off = w.lu_off = off;

@@ -42,16 +42,19 @@ def _digest(flags) -> str:
     return h.hexdigest()[:16]
 
 
-def build(variants=("fast", "strict"), verbose=False, jobs=None) -> list[str]:
+def build(variants=("fast", "strict"), verbose=False, jobs=None, extra_flags=(), suffix="") -> list[str]:
+    """`extra_flags` + `suffix` build an experiment next to the product libraries (e.g. extra_flags=["-DMCMC_STEP_UNROLL=2"],
+    suffix="_u2" -> libmcmc_b200_u2.so, objects under build/fast_u2/); load it with MCMC_B200_LIB=<path>."""
     if not os.path.exists(NVCC):
         raise RuntimeError(f"nvcc not found at {NVCC}")
     jobs = jobs or max(1, (os.cpu_count() or 4))
     outs = []
     for var in variants:
         vflags, libname = VARIANTS[var]
-        flags = BASE + vflags
+        flags = BASE + vflags + list(extra_flags)
         tag = _digest(flags)
-        odir = os.path.join(HERE, "build", var)
+        odir = os.path.join(HERE, "build", var + suffix)
+        libname = libname.replace(".so", suffix + ".so")
         os.makedirs(odir, exist_ok=True)
         lib = os.path.join(HERE, libname)
         stamp = os.path.join(odir, "digest.txt")
@@ -82,6 +85,14 @@ def build(variants=("fast", "strict"), verbose=False, jobs=None) -> list[str]:
 
 
 if __name__ == "__main__":
-    vs = tuple(sys.argv[1:]) or ("fast", "strict")
-    for p in build(vs, verbose=True):
+    # python -m mcmc_b200.csrc.build [fast|strict ...] [--suffix _x -DFOO=1 ...]
+    argv = sys.argv[1:]
+    sfx = ""
+    if "--suffix" in argv:
+        i = argv.index("--suffix")
+        sfx = argv[i + 1]
+        del argv[i:i + 2]
+    extra = [a for a in argv if a.startswith("-")]
+    vs = tuple(a for a in argv if not a.startswith("-")) or (("fast",) if sfx else ("fast", "strict"))
+    for p in build(vs, verbose=True, extra_flags=extra, suffix=sfx):
         print(p)

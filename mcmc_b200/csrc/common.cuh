@@ -37,6 +37,22 @@ struct Launch {
 };
 
 // jnp.minimum propagates NaN; fmin() does not.
+// Long sums (kinetic energy, log-density values, U-turn dot products) are serial DFMA chains: D dependent
+// latencies per sum, which is what a NUTS trip with few active lanes waits for.  The fast build keeps kSumWays
+// interleaved partial sums (d % kSumWays) and adds them pairwise; the strict build keeps the reference's
+// left-to-right order (kSumWays == 1).
+#if MCMC_IS_FAITHFUL
+constexpr int kSumWays = 1;
+#else
+constexpr int kSumWays = 4;
+#endif
+__device__ __forceinline__ double sum_ways(const double (&p)[kSumWays]) {
+  if (kSumWays == 4) return (p[0] + p[1 % kSumWays]) + (p[2 % kSumWays] + p[3 % kSumWays]);
+  double s = p[0];
+  for (int i = 1; i < kSumWays; ++i) s += p[i];
+  return s;
+}
+
 __device__ __forceinline__ double min_nan(double a, double b) {
   return (a != a) ? a : ((b != b) ? b : (a < b ? a : b));
 }
@@ -60,8 +76,8 @@ template <int TID> int launch_target_eval(const McmcParams& p, const double* cov
 
 // workspace layouts (bytes), shared by the launchers and mcmc_workspace_bytes
 struct NutsWs {
-  size_t cpad;       // chains padded to whole warps of 64
-  size_t slots_off, lp_off, acc_off, z_off, lu_off, total;
+  int64_t max_warps; // resident one-warp blocks the runtime-D lane tiles are sized for
+  size_t slots_off, home_off, lp_off, acc_off, queue_off, z_off, lu_off, total;
   int64_t tseg;      // iterations per segment of the native draw buffer
 };
 NutsWs nuts_ws_layout(const McmcParams& p);

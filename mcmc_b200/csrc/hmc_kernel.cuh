@@ -59,8 +59,8 @@ __device__ __forceinline__ double friction_gamma_dev(int sched, double t, double
 template <int DS, int BLOCK>
 struct HmcSmem {
   int n, L, tabn;
-  bool staged;
-  __host__ __device__ HmcSmem(int n_, int L_, int tabn_, bool staged_) : n(n_), L(L_), tabn(tabn_), staged(staged_) {}
+  bool welf;  // per-chain Welford tiles resident (MCMC_FLAG_ACCUM_WELFORD)
+  __host__ __device__ HmcSmem(int n_, int L_, int tabn_, bool welf_) : n(n_), L(L_), tabn(tabn_), welf(welf_) {}
   __host__ __device__ size_t off_w() const { return 0; }
   __host__ __device__ size_t off_epsw() const { return (size_t)n; }
   __host__ __device__ size_t off_sqw() const { return 2 * (size_t)n; }
@@ -71,12 +71,15 @@ struct HmcSmem {
   __host__ __device__ size_t off_tab() const { return off_logtab() + kRngTableDoubles; }
   __host__ __device__ size_t off_q() const { return ((off_tab() + (size_t)tabn + 1) / 2) * 2; }
   __host__ __device__ size_t off_g() const { return off_q() + (size_t)n * BLOCK; }
-  __host__ __device__ size_t off_stage() const { return off_g() + (size_t)n * BLOCK; }
-  __host__ __device__ size_t total_doubles() const { return off_stage(); }
+  __host__ __device__ size_t off_wm() const { return off_g() + (size_t)n * BLOCK; }  // Welford mean [d][tid]
+  __host__ __device__ size_t off_w2() const { return off_wm() + (welf ? (size_t)n * BLOCK : 0); }
+  __host__ __device__ size_t total_doubles() const { return off_w2() + (welf ? (size_t)n * BLOCK : 0); }
 };
 
-template <int TID, int DS, bool FRICTION, int BLOCK, int MINB = 1>
-__global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
+// WELF: the per-chain Welford accumulation (tuning batches) is compiled only into its own instantiation, so that the
+// sampling kernel's register allocation does not depend on it
+template <int TID, int DS, bool FRICTION, int BLOCK, bool WELF = false>
+__global__ void __launch_bounds__(BLOCK, 1) hmc_kernel(const HmcKArgs a) {
   constexpr int N = DS > 0 ? DS : MCMC_DYN_MAXD;
   const int n = DS > 0 ? DS : a.p.n_dim;
   const int L = a.p.num_steps;
@@ -85,11 +88,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
   const int tid = threadIdx.x;
   const bool store = !(a.p.flags & MCMC_FLAG_NO_SAMPLES) && a.b.samples != nullptr;
   const bool track = (a.p.flags & MCMC_FLAG_TRACK_PROPOSALS) != 0;
-  const bool do_w = (a.p.flags & MCMC_FLAG_ACCUM_WELFORD) && a.b.welford_mean && a.b.welford_m2;
+  constexpr bool do_w = WELF;
   const bool injected = a.p.rng_mode == MCMC_RNG_INJECTED;
 
   extern __shared__ __align__(16) double smem[];
-  const HmcSmem<DS, BLOCK> lay(n, L, target_table_len(TID, n), store);
+  const HmcSmem<DS, BLOCK> lay(n, L, target_table_len(TID, n), do_w);
   double* sm_w = smem + lay.off_w();
   double* sm_epsw = smem + lay.off_epsw();
   double* sm_sqw = smem + lay.off_sqw();
@@ -99,6 +102,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
   double* sm_tab = smem + lay.off_tab();
   double* sm_q = smem + lay.off_q();
   double* sm_g = smem + lay.off_g();
+  double* sm_wm = smem + lay.off_wm();
+  double* sm_w2 = smem + lay.off_w2();
 
   const double eps = a.p.step_size;
   const double half_eps = 0.5 * eps;  // HMC.py:119 `half * step_sz`; GRAHMC.py:193
@@ -217,6 +222,18 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
     for (int d = 0; d < n; ++d) sm_g[d * BLOCK + tid] = g[d];
   }
   double wcount = a.b.welford_count + (double)((it_begin > B) ? (it_begin - B) : 0);
+  if (do_w) {
+    // the group's Welford states stay in shared memory ([d][tid]) for the whole item: one coalesced read here, one
+    // coalesced write after the last iteration, instead of 4*D strided L2 accesses per chain and stored sample
+    const double* gm = a.b.welford_mean + chain0 * n;
+    const double* g2 = a.b.welford_m2 + chain0 * n;
+    for (int k = tid; k < nvalid * n; k += BLOCK) {
+      const int r = k / n, d = k - r * n;
+      sm_wm[d * BLOCK + r] = __ldcg(gm + k);  // L2: another SM may have run the previous chunk
+      sm_w2[d * BLOCK + r] = __ldcg(g2 + k);
+    }
+    __syncthreads();
+  }
 
   for (int64_t it = it_begin; it < it_end; ++it) {
     if (it == B) acc = 0;  // HMC.py:276-282
@@ -358,23 +375,38 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
         }
         if (active && a.b.log_probs) a.b.log_probs[(size_t)si * C + chain] = lp;
       }
-      if (do_w && active) {  // tuning/welford.py:42-59, one fold per stored sample (adaptation.py:229-235)
+      if (do_w) {  // tuning/welford.py:42-59, one fold per stored sample (adaptation.py:229-235)
         if (!accept) load_row<DS>(q, my_q, n);
         wcount += 1.0;
-        double* wm = a.b.welford_mean + chain * n;
-        double* w2 = a.b.welford_m2 + chain * n;
+#if !MCMC_IS_FAITHFUL
+        const double rcount = 1.0 / wcount;
+#endif
 #pragma unroll
         for (int d = 0; d < n; ++d) {
-          const double mean = __ldcg(wm + d);  // L2: another SM may have run the previous chunk
+          const double mean = sm_wm[d * BLOCK + tid];
           const double delta = q[d] - mean;
+#if MCMC_IS_FAITHFUL
           const double mean2 = mean + delta / wcount;
-          __stcg(wm + d, mean2);
-          __stcg(w2 + d, __ldcg(w2 + d) + delta * (q[d] - mean2));
+#else
+          const double mean2 = fma(delta, rcount, mean);
+#endif
+          sm_wm[d * BLOCK + tid] = mean2;
+          sm_w2[d * BLOCK + tid] += delta * (q[d] - mean2);
         }
       }
     }
   }
   if (bulk && tid == 0) bulk_wait_all();
+  if (do_w) {
+    __syncthreads();
+    double* gm = a.b.welford_mean + chain0 * n;
+    double* g2 = a.b.welford_m2 + chain0 * n;
+    for (int k = tid; k < nvalid * n; k += BLOCK) {
+      const int r = k / n, d = k - r * n;
+      __stcg(gm + k, sm_wm[d * BLOCK + r]);
+      __stcg(g2 + k, sm_w2[d * BLOCK + r]);
+    }
+  }
 
   if (!last_chunk) {
     // ---- hand the group's state tiles to whoever takes its next chunk (flat coalesced copy of sm_q / sm_g)
@@ -417,17 +449,16 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
 }
 
 // host-side launcher for one (target, D-variant)
-template <int TID, int DS, bool FRICTION, int BLOCK, int MINB = 1>
-int launch_hmc_variant(const Launch& l) {
+template <int TID, int DS, bool FRICTION, int BLOCK, bool WELF>
+int launch_hmc_variant_w(const Launch& l) {
   HmcKArgs a;
   a.p = l.p;
   a.b = l.b;
   a.t = make_target_ctx(l.p, l.b.cov_inv);
   const int n = l.p.n_dim;
-  const bool store = !(l.p.flags & MCMC_FLAG_NO_SAMPLES) && l.b.samples != nullptr;
-  const HmcSmem<DS, BLOCK> lay(n, l.p.num_steps, target_table_len(TID, n), store);
+  const HmcSmem<DS, BLOCK> lay(n, l.p.num_steps, target_table_len(TID, n), WELF);
   const size_t smem = lay.total_doubles() * sizeof(double);
-  auto kern = hmc_kernel<TID, DS, FRICTION, BLOCK, MINB>;
+  auto kern = hmc_kernel<TID, DS, FRICTION, BLOCK, WELF>;
   if (smem > 227 * 1024) {
     set_error("hmc: %zu bytes of shared memory needed (D=%d, L=%d) exceed 227 KB", smem, n, l.p.num_steps);
     return MCMC_ENOTSUP;
@@ -484,6 +515,12 @@ int launch_hmc_variant(const Launch& l) {
   }
   kern<<<(unsigned)grid, BLOCK, smem, l.stream>>>(a);
   return cuda_fail(cudaGetLastError(), "hmc_kernel launch");
+}
+
+template <int TID, int DS, bool FRICTION, int BLOCK>
+int launch_hmc_variant(const Launch& l) {
+  const bool welf = (l.p.flags & MCMC_FLAG_ACCUM_WELFORD) && l.b.welford_mean && l.b.welford_m2;
+  return welf ? launch_hmc_variant_w<TID, DS, FRICTION, BLOCK, true>(l) : launch_hmc_variant_w<TID, DS, FRICTION, BLOCK, false>(l);
 }
 
 }  // namespace mcmc

@@ -387,11 +387,12 @@ __global__ void __launch_bounds__(kWsThreads, 1) hmc_ws_kernel(const HmcKArgs a)
           wcount += 1.0;
           double* wm = a.b.welford_mean + chain * n;
           double* w2 = a.b.welford_m2 + chain * n;
+          const double rcount = 1.0 / wcount;  // same rounding sequence as hmc_kernel (fast build)
 #pragma unroll
           for (int d = 0; d < n; ++d) {
             const double mean = __ldcg(wm + d);
             const double delta = q[d] - mean;
-            const double mean2 = mean + delta / wcount;
+            const double mean2 = MCMC_IS_FAITHFUL ? mean + delta / wcount : fma(delta, rcount, mean);
             __stcg(wm + d, mean2);
             __stcg(w2 + d, __ldcg(w2 + d) + delta * (q[d] - mean2));
           }

@@ -14,11 +14,19 @@
 // divergent part.  Lane utilisation is then set by the total work per chain
 // (which concentrates over many transitions), not by the per-transition maximum.
 //
-// Tree ends (left/right q,p,g) and the proposal (q,g) are 8 D-vectors per chain.  They live in a
-// global workspace, one contiguous [slot][d][lane] tile per warp (coalesced, constant offsets,
-// L2-resident): in shared memory they capped the SM at 5 warps, in L2 the kernel is limited by
-// registers only (8 warps per SM).  The end integrated last stays in registers and is written back
-// only when the tree turns round, so a subtree boundary costs one read of the opposite end.
+// Memory per chain in flight: the working tree end (q, p, g: the end integrated last) stays in registers; the
+// opposite end (q, p, g) and the proposal (q, g) are five D-vectors in a [slot][d][lane] tile private to the LANE — in
+// shared memory for the compiled dimensions (25.6 KB per warp at D=20: eight one-warp blocks per SM, the register
+// limit), in an L2-resident workspace tile for the runtime-D variant.  A subtree boundary (U-turn test, turn-round,
+// proposal swap) therefore never leaves the SM.
+//
+// Work distribution: a chain is not tied to a lane.  The run is cut into chunks of iterations; items (chunk, chain)
+// are claimed chunk-major from an atomic counter by whichever lane runs out of work, the chain's state (q, g, lp,
+// accept counter) travels between items through a per-chain home row in the workspace, and an item whose
+// predecessor is still running parks its lane in a WAIT state that is polled once per loop trip (the other lanes
+// keep stepping).  With a fixed lane->chain map a warp ran until its slowest chain finished: on the 20-D
+// rosenbrock 30% and on Neal's funnel 75% of all lane-steps were idle tail (tools/nuts_tail_probe.py).  Results do
+// not depend on who runs which item: every random number is keyed on (global chain, absolute iteration).
 //
 // Native random stream: the momenta and the slice uniform of every (chain, iteration) are drawn by a
 // separate, fully convergent kernel (nuts_rng_fill_kernel, abi.cu) into the workspace with the SAME
@@ -40,26 +48,41 @@ struct NutsKArgs {
   McmcBuffers b;
   TargetCtx t;
   int64_t it_begin, it_end;   // absolute iterations [it_begin, it_end) of this launch (segment)
-  double* slots;              // [SL_COUNT][D][cpad]
-  size_t cpad;
-  double* carry_lp;           // [cpad] log-prob of the current state between segments
-  int* carry_acc;             // [cpad]
+  double* slots;              // runtime-D variant only: [resident warp][SL_COUNT][D][32] lane tiles
+  double* home;               // [C][2D]: (q, g) of every chain's current state between items / launches
+  double* home_lp;            // [C]
+  int* home_acc;              // [C]
+  unsigned int* queue;        // item counter of this launch
+  unsigned int* flags;        // [C] chunks of this launch completed, per chain
+  int chunk_iters, n_chunks;
   const double* z;            // momenta draws: z_inject (+ it*C*D) or the filled segment buffer
   const double* logu;         // native stream: log of the slice uniform per (segment iteration, chain); else NULL
   int64_t z_it0;              // iteration that row 0 of z / logu corresponds to
 };
 
-enum { SL_QL = 0, SL_PL, SL_GL, SL_QR, SL_PR, SL_GR, SL_QP, SL_GP, SL_COUNT };
+// other tree end (q, p, g) and proposal (q, g)
+enum { SL_QO = 0, SL_PO, SL_GO, SL_QP, SL_GP, SL_COUNT };
+
+#ifndef MCMC_NUTS_MINBLOCKS
+#define MCMC_NUTS_MINBLOCKS 1
+#endif
+constexpr int kNutsMinBlocks = MCMC_NUTS_MINBLOCKS;
+#ifndef MCMC_NUTS_BK_TRIPS
+#define MCMC_NUTS_BK_TRIPS 8
+#endif
+#ifndef MCMC_NUTS_BK_LANES
+#define MCMC_NUTS_BK_LANES 16
+#endif
+constexpr int kNutsBkTrips = MCMC_NUTS_BK_TRIPS, kNutsBkLanes = MCMC_NUTS_BK_LANES;
 
 template <int TID, int DS, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
+__global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kernel(const NutsKArgs a) {
+  static_assert(BLOCK == 32, "one warp per block: the lane tiles are sized per block");
   constexpr int N = DS > 0 ? DS : MCMC_DYN_MAXD;
+  constexpr bool kSmemSlots = DS > 0;
   const int n = DS > 0 ? DS : a.p.n_dim;
   const int64_t C = a.p.n_chains, S = a.p.num_samples, B = a.p.burn_in;
   const int tid = threadIdx.x;
-  const int64_t chain0 = (int64_t)blockIdx.x * BLOCK;
-  const bool active = chain0 + tid < C;
-  const int64_t chain = active ? chain0 + tid : C - 1;
   const bool store = !(a.p.flags & MCMC_FLAG_NO_SAMPLES) && a.b.samples != nullptr;
   const bool do_w = (a.p.flags & MCMC_FLAG_ACCUM_WELFORD) && a.b.welford_mean && a.b.welford_m2;
   const bool injected = a.p.rng_mode == MCMC_RNG_INJECTED;
@@ -71,9 +94,10 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
   double* sm_w = smem;
   double* sm_sqw = smem + n;
   double* sm_tab = smem + 2 * n;
-  // Slots of one warp are a contiguous [slot][d][lane] tile: slot(s, d) = wbase[(s*n + d)*32], i.e. every
-  // access is one coalesced 256-byte request at a compile-time offset from a per-lane base pointer.
-  double* wbase = a.slots + (size_t)((chain0 + tid) >> 5) * ((size_t)SL_COUNT * n * 32) + (tid & 31);
+  // lane tile: slot(s, d) = wbase[(s*n + d)*32] — conflict-free in shared memory, one coalesced 256-byte request in L2
+  double* wbase;
+  if (kSmemSlots) wbase = smem + ((2 * n + target_table_len(TID, n) + 1) / 2) * 2 + tid;
+  else wbase = a.slots + (size_t)blockIdx.x * ((size_t)SL_COUNT * n * 32) + tid;
 #define SLOT(s, d) wbase[((s) * n + (d)) * 32]
 
   for (int d = tid; d < n; d += BLOCK) {
@@ -89,49 +113,87 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
   __syncthreads();
 
   RngCtx rng;
-  {
-    const uint64_t gid = (uint64_t)(a.p.chain_offset + chain);
-    rng.k0 = a.p.seed[0]; rng.k1 = a.p.seed[1];
-    rng.gid_lo = (uint32_t)gid; rng.gid_hi = (uint32_t)(gid >> 32);
-    rng.logtab = nullptr;   // only the integer-valued direction / proposal uniforms are drawn in this kernel
-  }
+  rng.k0 = a.p.seed[0]; rng.k1 = a.p.seed[1];
+  rng.gid_lo = rng.gid_hi = 0;
+  rng.logtab = nullptr;   // only the integer-valued direction / proposal uniforms are drawn in this kernel
 
-  // Working point = the tree end that was integrated last (direction reg_dir).  It stays in registers; its slot
-  // is written only when the tree turns round, the opposite end is always current in its slot.
+  // Working point = the tree end that was integrated last (direction reg_dir).  It stays in registers; the
+  // opposite end is always current in the O slots and the two are swapped when the tree turns round.
   double qs[N], ps[N], gs[N];
   double lps = 0.0;
-
-  // nuts_init (NUTS.py:73-86): the current state lives in the proposal slots; a later segment of the
-  // same run finds it there and picks up the carried log-prob / accept counter
-  double lpp;
+  double lpp = 0.0;
   int acc = 0;
-  if (a.it_begin == 0) {
-    const double* src = a.b.init_q + chain * n;
-#pragma unroll
-    for (int d = 0; d < n; ++d) qs[d] = src[d];
-    lpp = target_eval<TID, DS, true, true>(a.t, n, qs, gs, sm_tab);
-#pragma unroll
-    for (int d = 0; d < n; ++d) {
-      SLOT(SL_QP, d) = qs[d];
-      SLOT(SL_GP, d) = gs[d];
-    }
-  } else {
-    lpp = a.carry_lp[chain0 + tid];
-    acc = a.carry_acc[chain0 + tid];
-  }
 
   // per-transition scalars
   double h0 = 0.0, log_u = 0.0, sum_alpha = 0.0, sa = 0.0, h_new = 0.0, u_prop = 0.0;
   double se = 0.0, hse = 0.0;
   int n_valid = 1, n_steps = 0, depth = 0, direction = 1, reg_dir = 1, k = 0, num_steps = 0;
-  bool diverged = false, in_subtree = false, in_transition = false, done = a.it_begin >= a.it_end;
-  int64_t it = a.it_begin;
-  double wcount = a.b.welford_count + (double)(a.it_begin > B ? a.it_begin - B : 0);
-  unsigned long long n_grad = 0, sum_depth = 0, n_div = 0;
+  bool diverged = false, in_subtree = false, in_transition = false;
+  // per-item state
+  bool done = false, have_item = false, waiting = false;
+  int64_t it = 0, it_item_end = 0, chain = 0;
+  unsigned int chunk = 0;
+  double wcount = 0.0;
+  unsigned long long n_grad = 0, sum_depth = 0, n_div = 0, acc_total = 0;
+  const unsigned int n_items = (unsigned int)C * (unsigned int)a.n_chunks;
 
+  int since_bk = 0;
   while (!__all_sync(0xffffffffu, done)) {
-    // ------------------------------------------------------------ bookkeeping (divergent, kept short)
-    while (k == 0 && !done) {
+    // ------------------------------------------------------------ bookkeeping (divergent, latency-bound)
+    // A trip that runs it costs several times a leapfrog step in dependent-latency, whether one lane needs it or
+    // all 32 do.  So it is batched: lanes whose subtree ended idle until kNutsBkLanes of them are waiting, the
+    // oldest has waited kNutsBkTrips trips, or nobody has a step left.  Purely a schedule: results are unchanged.
+    const unsigned int needy = __ballot_sync(0xffffffffu, k == 0 && !done);
+    const unsigned int busy = __ballot_sync(0xffffffffu, k > 0);
+    since_bk += 1;
+    const bool run_bk = needy && (busy == 0u || __popc(needy) >= kNutsBkLanes || since_bk >= kNutsBkTrips);
+    if (run_bk) since_bk = 0;
+    while (run_bk && k == 0 && !done) {
+      if (!have_item) {
+        if (!waiting) {
+          const unsigned int id = atomicAdd(a.queue, 1u);
+          if (id >= n_items) { done = true; break; }
+          chunk = id / (unsigned int)C;
+          chain = (int64_t)(id - chunk * (unsigned int)C);
+          it = a.it_begin + (int64_t)chunk * a.chunk_iters;
+          it_item_end = (it + a.chunk_iters < a.it_end) ? it + a.chunk_iters : a.it_end;
+          waiting = chunk > 0;
+        }
+        if (waiting) {
+          // the chain's previous chunk is still running on another lane: look again next trip
+          if (ld_acquire_u32(a.flags + chain) < chunk) break;
+          waiting = false;
+        }
+        const uint64_t gid = (uint64_t)(a.p.chain_offset + chain);
+        rng.gid_lo = (uint32_t)gid; rng.gid_hi = (uint32_t)(gid >> 32);
+        if (it == 0) {
+          // nuts_init (NUTS.py:73-86): value and gradient at the initial position
+          const double* src = a.b.init_q + chain * n;
+#pragma unroll
+          for (int d = 0; d < n; ++d) qs[d] = src[d];
+          lpp = target_eval<TID, DS, true, true>(a.t, n, qs, gs, sm_tab);
+          acc = 0;
+#pragma unroll
+          for (int d = 0; d < n; ++d) {
+            SLOT(SL_QP, d) = qs[d];
+            SLOT(SL_GP, d) = gs[d];
+          }
+        } else {
+          // state left by the previous item of this chain (another lane, another SM or the previous launch)
+          const double* hq = a.home + (size_t)chain * 2 * n;
+#pragma unroll
+          for (int d = 0; d < n; ++d) {
+            SLOT(SL_QP, d) = __ldcg(hq + d);
+            SLOT(SL_GP, d) = __ldcg(hq + n + d);
+          }
+          lpp = __ldcg(a.home_lp + chain);
+          acc = __ldcg(a.home_acc + chain);
+        }
+        wcount = a.b.welford_count + (double)(it > B ? it - B : 0);
+        have_item = true;
+        in_transition = false;
+        in_subtree = false;
+      }
       bool u_turn = false;
       if (in_subtree) {
         // subtree endpoint: validity, divergence, proposal swap (NUTS.py:281-378); the new end stays in registers
@@ -158,28 +220,28 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
         depth += 1;
         diverged = diverged || is_div;
         in_subtree = false;
-        // cond_fn (NUTS.py:243-248) on (q_right - q_left) . p_left / p_right; NaN compares false -> no U-turn
-        const double* oth = wbase + (reg_dir > 0 ? SL_QL : SL_QR) * n * 32;
-        // with e = q_work - q_other:  working end on the right: (dl, dr) = (e.p_other, e.p_work);
+        // cond_fn (NUTS.py:243-248) on (q_right - q_left) . p_left / p_right; NaN compares false -> no U-turn.
+        // With e = q_work - q_other:  working end on the right: (dl, dr) = (e.p_other, e.p_work);
         // on the left q_right - q_left = -e: (dl, dr) = (-(e.p_work), -(e.p_other)) — negation commutes with
         // every rounding, so this is the reference's value bit for bit
-        double eo = 0.0, ew = 0.0;
+        double eop[kSumWays] = {0.0}, ewp[kSumWays] = {0.0};
 #pragma unroll
         for (int d = 0; d < n; ++d) {
-          const double e = qs[d] - oth[d * 32];
-          eo += e * oth[(n + d) * 32];
-          ew += e * ps[d];
+          const double e = qs[d] - SLOT(SL_QO, d);
+          eop[d % kSumWays] += e * SLOT(SL_PO, d);
+          ewp[d % kSumWays] += e * ps[d];
         }
+        const double eo = sum_ways(eop), ew = sum_ways(ewp);
         const double dl = reg_dir > 0 ? eo : -ew, dr = reg_dir > 0 ? ew : -eo;
         u_turn = (dl < 0) | (dr < 0);
       }
       if (!in_transition) {
         // new transition: momentum, energy, slice (NUTS.py:217-241).  Both tree ends are the current state
-        // (q_prop, p0, g_prop): it is loaded into the working registers; the end opposite to the first
-        // direction is written once that direction is known (below).  q_left == q_right -> no U-turn yet.
+        // (q_prop, p0, g_prop): it is loaded into the working registers and copied to the O slots once the
+        // first direction is known (below).  q_left == q_right -> no U-turn yet.
         if (it == B) acc = 0;  // NUTS.py:494-500
         load_row<DS>(ps, a.z + ((size_t)(it - a.z_it0) * C + chain) * n, n);
-        double kin = 0.0;
+        double kinp[kSumWays] = {0.0};
 #pragma unroll
         for (int d = 0; d < n; ++d) {
 #if MCMC_IS_FAITHFUL
@@ -187,11 +249,11 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
 #else
           ps[d] = ps[d] * sm_sqw[d];
 #endif
-          kin += (ps[d] * ps[d]) * sm_w[d];
+          kinp[d % kSumWays] += (ps[d] * ps[d]) * sm_w[d];
           qs[d] = SLOT(SL_QP, d);
           gs[d] = SLOT(SL_GP, d);
         }
-        h0 = -lpp + 0.5 * kin;
+        h0 = -lpp + 0.5 * sum_ways(kinp);
         const double lgu = a.logu ? a.logu[(size_t)(it - a.z_it0) * C + chain] : log(a.b.u_inject[(size_t)it * C + chain]);
         log_u = lgu - h0;
         n_valid = 1; n_steps = 0; sum_alpha = 0.0; depth = 0; diverged = false;
@@ -211,26 +273,22 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
         }
         direction = (u_dir < 0.5) ? 1 : -1;  // bernoulli(0.5) = uniform < 0.5
         if (reg_dir == 0) {
-          // first subtree of the transition: the initial state becomes the end opposite to `direction`
-          double* oth = wbase + (direction > 0 ? SL_QL : SL_QR) * n * 32;
+          // first subtree of the transition: the initial state is also the end opposite to `direction`
 #pragma unroll
           for (int d = 0; d < n; ++d) {
-            oth[d * 32] = qs[d];
-            oth[(n + d) * 32] = ps[d];
-            oth[(2 * n + d) * 32] = gs[d];
+            SLOT(SL_QO, d) = qs[d];
+            SLOT(SL_PO, d) = ps[d];
+            SLOT(SL_GO, d) = gs[d];
           }
         } else if (direction != reg_dir) {
-          // the tree turns round: park the working end, fetch the opposite one
-          double* mine = wbase + (reg_dir > 0 ? SL_QR : SL_QL) * n * 32;
-          const double* oth = wbase + (direction > 0 ? SL_QR : SL_QL) * n * 32;
+          // the tree turns round: the working end and the opposite end change places
 #pragma unroll
           for (int d = 0; d < n; ++d) {
-            mine[d * 32] = qs[d];
-            mine[(n + d) * 32] = ps[d];
-            mine[(2 * n + d) * 32] = gs[d];
-            qs[d] = oth[d * 32];
-            ps[d] = oth[(n + d) * 32];
-            gs[d] = oth[(2 * n + d) * 32];
+            const double tq = SLOT(SL_QO, d), tp = SLOT(SL_PO, d), tg = SLOT(SL_GO, d);
+            SLOT(SL_QO, d) = qs[d];
+            SLOT(SL_PO, d) = ps[d];
+            SLOT(SL_GO, d) = gs[d];
+            qs[d] = tq; ps[d] = tp; gs[d] = tg;
           }
         }
         reg_dir = direction;
@@ -249,7 +307,7 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
         sum_depth += (unsigned long long)depth;
         n_div += diverged ? 1ull : 0ull;
         const int64_t si = it - B;
-        if (si >= 0 && active) {
+        if (si >= 0) {
           const size_t o = (size_t)si * C + chain;
           if (store || do_w) {
 #pragma unroll
@@ -261,70 +319,89 @@ __global__ void __launch_bounds__(BLOCK) nuts_kernel(const NutsKArgs a) {
           }
           if (a.b.tree_depths) a.b.tree_depths[o] = depth;
           if (a.b.mean_accept_probs) a.b.mean_accept_probs[o] = map;
-          if (do_w) {
+          if (do_w) {  // tuning/welford.py:42-59; L2 accesses: the previous item of the chain may have run on another SM
             wcount += 1.0;
             double* wm = a.b.welford_mean + chain * n;
             double* w2 = a.b.welford_m2 + chain * n;
+#if !MCMC_IS_FAITHFUL
+            const double rcount = 1.0 / wcount;
+#endif
 #pragma unroll
             for (int d = 0; d < n; ++d) {
-              const double mean = wm[d];
+              const double mean = __ldcg(wm + d);
               const double delta = qs[d] - mean;
+#if MCMC_IS_FAITHFUL
               const double mean2 = mean + delta / wcount;
-              wm[d] = mean2;
-              w2[d] = w2[d] + delta * (qs[d] - mean2);
+#else
+              const double mean2 = fma(delta, rcount, mean);
+#endif
+              __stcg(wm + d, mean2);
+              __stcg(w2 + d, __ldcg(w2 + d) + delta * (qs[d] - mean2));
             }
           }
         }
         in_transition = false;
         it += 1;
-        if (it == a.it_end) done = true;
+        if (it == it_item_end) {
+          // ---- item finished: the chain's state goes home (or, after the last iteration, to the outputs)
+          if (it == B + S) {
+            acc_total += (unsigned long long)acc;
+            if (a.b.accept_count) a.b.accept_count[chain] = acc;
+            if (a.b.accept_rate) a.b.accept_rate[chain] = (float)acc / (float)S;  // NUTS.py:512
+            if (a.b.final_lp) a.b.final_lp[chain] = lpp;
+            if (a.b.final_q || a.b.final_g) {
+#pragma unroll
+              for (int d = 0; d < n; ++d) {
+                qs[d] = SLOT(SL_QP, d);
+                gs[d] = SLOT(SL_GP, d);
+              }
+              if (a.b.final_q) store_row<DS>(a.b.final_q + chain * n, qs, n);
+              if (a.b.final_g) store_row<DS>(a.b.final_g + chain * n, gs, n);
+            }
+          } else {
+            double* hq = a.home + (size_t)chain * 2 * n;
+#pragma unroll
+            for (int d = 0; d < n; ++d) {
+              __stcg(hq + d, SLOT(SL_QP, d));
+              __stcg(hq + n + d, SLOT(SL_GP, d));
+            }
+            __stcg(a.home_lp + chain, lpp);
+            __stcg(a.home_acc + chain, acc);
+            __threadfence();
+            st_release_u32(a.flags + chain, chunk + 1u);
+          }
+          have_item = false;
+        }
       }
     }
 
     // ------------------------------------------------------------ one leapfrog step (convergent, hot)
-    if (!done) {
+    if (k > 0) {
 #pragma unroll
       for (int d = 0; d < n; ++d) {
         ps[d] = ps[d] + hse * gs[d];              // NUTS.py:107
         qs[d] = qs[d] + se * (ps[d] * sm_w[d]);   // NUTS.py:109
       }
       lps = target_eval<TID, DS, true, true>(a.t, n, qs, gs, sm_tab);  // NUTS.py:111
-      double kin = 0.0;
+      double kinp[kSumWays] = {0.0};
 #pragma unroll
       for (int d = 0; d < n; ++d) {
         ps[d] = ps[d] + hse * gs[d];              // NUTS.py:115
-        kin += (ps[d] * ps[d]) * sm_w[d];
+        kinp[d % kSumWays] += (ps[d] * ps[d]) * sm_w[d];
       }
-      h_new = -lps + 0.5 * kin;                   // NUTS.py:178 / :282
+      h_new = -lps + 0.5 * sum_ways(kinp);        // NUTS.py:178 / :282
       sa = sa + exp_nonpos(min_nan(0.0, h0 - h_new));    // NUTS.py:179-181
       k -= 1;
-    }
-  }
-
-  if (a.it_end < B + S) {
-    a.carry_lp[chain0 + tid] = lpp;
-    a.carry_acc[chain0 + tid] = acc;
-  } else if (active) {
-    if (a.b.accept_count) a.b.accept_count[chain] = acc;
-    if (a.b.accept_rate) a.b.accept_rate[chain] = (float)acc / (float)S;  // NUTS.py:512
-    if (a.b.final_lp) a.b.final_lp[chain] = lpp;
-    if (a.b.final_q || a.b.final_g) {
-#pragma unroll
-      for (int d = 0; d < n; ++d) {
-        qs[d] = SLOT(SL_QP, d);
-        gs[d] = SLOT(SL_GP, d);
-      }
-      if (a.b.final_q) store_row<DS>(a.b.final_q + chain * n, qs, n);
-      if (a.b.final_g) store_row<DS>(a.b.final_g + chain * n, gs, n);
+    } else if (__activemask() == 0xffffffffu) {
+      __nanosleep(100);  // every lane of the warp is waiting for another warp's item (or finished)
     }
   }
 #undef SLOT
   if (a.b.counters) {
-    if (!active) { acc = 0; n_grad = 0; sum_depth = 0; n_div = 0; }
-    if (a.it_end == B + S) atomicAdd(a.b.counters + 0, (unsigned long long)acc);
-    atomicAdd(a.b.counters + 1, n_grad);
-    atomicAdd(a.b.counters + 2, sum_depth);
-    atomicAdd(a.b.counters + 3, n_div);
+    if (acc_total) atomicAdd(a.b.counters + 0, acc_total);
+    if (n_grad) atomicAdd(a.b.counters + 1, n_grad);
+    if (sum_depth) atomicAdd(a.b.counters + 2, sum_depth);
+    if (n_div) atomicAdd(a.b.counters + 3, n_div);
   }
 }
 
@@ -336,7 +413,8 @@ int launch_nuts_variant(const Launch& l) {
   a.t = make_target_ctx(l.p, l.b.cov_inv);
   const int n = l.p.n_dim;
   const int tabn = target_table_len(TID, n);
-  const size_t smem = (size_t)(2 * n + tabn) * sizeof(double);
+  const size_t tile = (size_t)SL_COUNT * n * 32;   // doubles per warp
+  const size_t smem = ((size_t)((2 * n + tabn + 1) / 2) * 2 + (DS > 0 ? tile : 0)) * sizeof(double);
   const NutsWs ws = nuts_ws_layout(l.p);
   if (!l.b.workspace || l.b.workspace_bytes < ws.total) {
     set_error("nuts: workspace of %zu bytes required (got %zu)", ws.total, l.b.workspace_bytes);
@@ -350,21 +428,50 @@ int launch_nuts_variant(const Launch& l) {
   if (int rc = cuda_fail(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                          "cudaFuncSetAttribute(nuts)"))
     return rc;
-  const int64_t grid = (l.p.n_chains + BLOCK - 1) / BLOCK;
-  if (grid == 0) return MCMC_OK;
+  const int64_t C = l.p.n_chains;
+  if (C == 0) return MCMC_OK;
+  if (C >= ((int64_t)1 << 31)) { set_error("nuts: more than 2^31 chains"); return MCMC_ENOTSUP; }
+  // persistent one-warp blocks: as many as fit (at most ws.max_warps, which sized the runtime-D lane tiles)
+  int per_sm = 0;
+  if (int rc = cuda_fail(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, BLOCK, smem), "occupancy(nuts)"))
+    return rc;
+  int64_t grid = (int64_t)per_sm * device_sm_count();
+  if (grid > ws.max_warps) grid = ws.max_warps;
+  if (grid > (C + 31) / 32) grid = (C + 31) / 32;
+  if (grid < 1) grid = 1;
   char* w = reinterpret_cast<char*>(l.b.workspace);
   a.slots = reinterpret_cast<double*>(w + ws.slots_off);
-  a.cpad = ws.cpad;
-  a.carry_lp = reinterpret_cast<double*>(w + ws.lp_off);
-  a.carry_acc = reinterpret_cast<int*>(w + ws.acc_off);
+  a.home = reinterpret_cast<double*>(w + ws.home_off);
+  a.home_lp = reinterpret_cast<double*>(w + ws.lp_off);
+  a.home_acc = reinterpret_cast<int*>(w + ws.acc_off);
+  a.queue = reinterpret_cast<unsigned int*>(w + ws.queue_off);
+  a.flags = a.queue + 64;
   const int64_t T = l.p.burn_in + l.p.num_samples;
   const bool native = l.p.rng_mode == MCMC_RNG_PHILOX;
+  const char* chunk_env = getenv("MCMC_NUTS_CHUNK");  // test hook / tuning knob: iterations per item
   // segments of at most ws.tseg iterations (one segment unless the draw buffer would exceed its cap)
   int64_t it0 = 0;
   do {
     const int64_t it1 = (native && it0 + ws.tseg < T) ? it0 + ws.tseg : T;
     a.it_begin = it0;
     a.it_end = it1;
+    // items: with more chains than resident lanes, ~12 chunks per chain keep the last wave of items a small tail;
+    // otherwise every chain has a lane of its own and one item per chain is all there is to do
+    int64_t ci = it1 - it0;
+    if (chunk_env && atoll(chunk_env) > 0) ci = atoll(chunk_env);
+    else if (C > grid * 32) ci = (it1 - it0 + 11) / 12;
+    if (ci < 1) ci = 1;
+    int64_t nch = (it1 - it0 + ci - 1) / ci;
+    if (nch * C >= ((int64_t)1 << 32) - (grid * 32 + 1)) {  // the queue counter is 32-bit: fall back to longer items
+      nch = (((int64_t)1 << 32) - (grid * 32 + 2)) / C;
+      if (nch < 1) nch = 1;
+      ci = (it1 - it0 + nch - 1) / nch;
+      nch = (it1 - it0 + ci - 1) / ci;
+    }
+    a.chunk_iters = (int)ci;
+    a.n_chunks = (int)nch;
+    if (int rc = cuda_fail(cudaMemsetAsync(a.queue, 0, (64 + (size_t)C) * sizeof(unsigned int), l.stream), "memset(nuts queue)"))
+      return rc;
     if (native) {
       double* zb = reinterpret_cast<double*>(w + ws.z_off);
       double* lb = reinterpret_cast<double*>(w + ws.lu_off);

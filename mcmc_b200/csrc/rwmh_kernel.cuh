@@ -18,8 +18,13 @@ struct RwmhKArgs {
   TargetCtx t;
 };
 
+#ifndef MCMC_RWMH_MINBLOCKS
+#define MCMC_RWMH_MINBLOCKS 1
+#endif
+constexpr int kRwmhMinBlocks = MCMC_RWMH_MINBLOCKS;
+
 template <int TID, int DS, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) rwmh_kernel(const RwmhKArgs a) {
+__global__ void __launch_bounds__(BLOCK, DS > 0 ? kRwmhMinBlocks : 1) rwmh_kernel(const RwmhKArgs a) {
   constexpr int N = DS > 0 ? DS : MCMC_DYN_MAXD;
   const int n = DS > 0 ? DS : a.p.n_dim;
   const int64_t C = a.p.n_chains, S = a.p.num_samples, B = a.p.burn_in;

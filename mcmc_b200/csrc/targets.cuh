@@ -108,13 +108,13 @@ __device__ __forceinline__ double target_eval(const TargetCtx& t, const int n_rt
   const int n = DS > 0 ? DS : n_rt;
   double lp = 0.0;
   if (TID == MCMC_TARGET_STANDARD_NORMAL) {
-    double s = 0.0;
+    double sp[kSumWays] = {0.0};
 #pragma unroll
     for (int d = 0; d < n; ++d) {
-      if (WANT_LP) s += q[d] * q[d];
+      if (WANT_LP) sp[d % kSumWays] += q[d] * q[d];
       if (WANT_G) g[d] = -q[d];
     }
-    if (WANT_LP) lp = -0.5 * (s + t.c[0]);
+    if (WANT_LP) lp = -0.5 * (sum_ways(sp) + t.c[0]);
   } else if (TID == MCMC_TARGET_CORRELATED_GAUSSIAN) {
     // P = a I + b J:  (x P)_j = a x_j + b sum(x); the reference forms the dense product
     // (targets.py:94), whose row sums reduce to this in exact arithmetic.
@@ -142,9 +142,10 @@ __device__ __forceinline__ double target_eval(const TargetCtx& t, const int n_rt
     if (WANT_LP) lp = -0.5 * (maha + t.c[0] + t.c[1]);
   } else if (TID == MCMC_TARGET_NEALS_FUNNEL) {
     const double x0 = q[0];
-    double s = 0.0;
+    double sp[kSumWays] = {0.0};
 #pragma unroll
-    for (int d = 1; d < n; ++d) s += q[d] * q[d];
+    for (int d = 1; d < n; ++d) sp[d % kSumWays] += q[d] * q[d];
+    const double s = sum_ways(sp);
 #if MCMC_IS_FAITHFUL
     const double var = exp(x0);
     const double sv = s / var;
@@ -221,13 +222,19 @@ __device__ __forceinline__ double target_eval(const TargetCtx& t, const int n_rt
     // 4 DFMA per coupling term: with t_i = x_{i+1} - x_i^2,
     //   g_i = 2(1 - x_i) + 4a x_i t_i - 2a t_{i-1} = x_i (4a t_i - 2) + 2 - 2a t_{i-1}
     double tprev = 0.0;
+    double Up[4] = {0.0, 0.0, 0.0, 0.0};  // four interleaved partial sums: the value's dependency chain is 4x shorter
 #pragma unroll
     for (int i = 0; i < n - 1; ++i) {
       const double ti = fma(-q[i], q[i], q[i + 1]);
       if (WANT_LP) {
         const double om = 1.0 - q[i];
-        U = fma(om, om, U);
-        U = fma(a * ti, ti, U);
+#ifdef MCMC_ROSEN_SERIAL_SUM
+        Up[0] = fma(om, om, Up[0]);
+        Up[0] = fma(a * ti, ti, Up[0]);
+#else
+        Up[i & 3] = fma(om, om, Up[i & 3]);
+        Up[(i + 2) & 3] = fma(a * ti, ti, Up[(i + 2) & 3]);
+#endif
       }
       if (WANT_G) {
         const double hi = fma(q[i], fma(a4, ti, -2.0), 2.0);
@@ -236,6 +243,7 @@ __device__ __forceinline__ double target_eval(const TargetCtx& t, const int n_rt
       }
     }
     if (WANT_G) g[n - 1] = (n > 1) ? am2 * tprev : 0.0;
+    if (WANT_LP) U = (Up[0] + Up[1]) + (Up[2] + Up[3]);
 #endif
     if (WANT_LP) lp = -U;
   } else if (TID == MCMC_TARGET_GAUSSIAN_MIXTURE) {
