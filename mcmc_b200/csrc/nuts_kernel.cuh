@@ -240,7 +240,13 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
         // (q_prop, p0, g_prop): it is loaded into the working registers and copied to the O slots once the
         // first direction is known (below).  q_left == q_right -> no U-turn yet.
         if (it == B) acc = 0;  // NUTS.py:494-500
-        load_row<DS>(ps, a.z + ((size_t)(it - a.z_it0) * C + chain) * n, n);
+        const double* zrow = a.z + ((size_t)(it - a.z_it0) * C + chain) * n;
+        load_row<DS>(ps, zrow, n);
+        if (it + 1 < it_item_end) {
+          // the next transition's draws (one row further in the segment buffer) start their way from HBM to L2 now
+          const char* nx = reinterpret_cast<const char*>(zrow + (size_t)C * n);
+          for (int o = 0; o < n * 8; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + o));
+        }
         double kinp[kSumWays] = {0.0};
 #pragma unroll
         for (int d = 0; d < n; ++d) {
@@ -455,11 +461,12 @@ int launch_nuts_variant(const Launch& l) {
     const int64_t it1 = (native && it0 + ws.tseg < T) ? it0 + ws.tseg : T;
     a.it_begin = it0;
     a.it_end = it1;
-    // items: with more chains than resident lanes, ~12 chunks per chain keep the last wave of items a small tail;
-    // otherwise every chain has a lane of its own and one item per chain is all there is to do
+    // items: with more chains than resident lanes, ~6 chunks per chain (measured optimum at 65,536 chains x 288
+    // iterations: 3..6 within 2%; more chunks add WAIT polling, fewer leave a longer tail); otherwise every chain
+    // has a lane of its own and one item per chain is all there is to do
     int64_t ci = it1 - it0;
     if (chunk_env && atoll(chunk_env) > 0) ci = atoll(chunk_env);
-    else if (C > grid * 32) ci = (it1 - it0 + 11) / 12;
+    else if (C > grid * 32) ci = (it1 - it0 + 5) / 6;
     if (ci < 1) ci = 1;
     int64_t nch = (it1 - it0 + ci - 1) / ci;
     if (nch * C >= ((int64_t)1 << 32) - (grid * 32 + 1)) {  // the queue counter is 32-bit: fall back to longer items

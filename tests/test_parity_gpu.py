@@ -255,6 +255,32 @@ def test_nuts_native_stream_segments_are_bit_identical(gpu_lib, oracle, monkeypa
         assert np.array_equal(ref[k], seg[k], equal_nan=True), k
 
 
+@pytest.mark.parametrize("name,D,eps", [("rosenbrock", 20, 0.03), ("neals_funnel", 20, 0.15), ("gaussian_mixture", 7, 0.2)])
+def test_nuts_items_claimed_per_lane_are_bit_identical(gpu_lib, oracle, monkeypatch, name, D, eps):
+    """A NUTS chain is not tied to a lane: (chunk of iterations, chain) items are claimed from a queue and the state
+    travels through the workspace, with lanes parked in a WAIT state while a predecessor item runs elsewhere.  Whatever
+    the chunk length (1 iteration: every transition changes hands; 4: ragged last chunk; default: one item per chain at
+    this size), compiled-D (shared-memory lane tiles) or runtime-D (L2 lane tiles), the outputs must not change a bit."""
+    C_, S, B = 300, 11, 2
+    q0 = np.random.default_rng(9).standard_normal((C_, D))
+    wf = (np.zeros((C_, D)), np.zeros((C_, D)))
+    par = [3.0] if name == "gaussian_mixture" else []
+    p = oracle.make_params(tid(name), par, C_, D, S, B, 0, eps, rng_mode=_abi.RNG_PHILOX, seed=(15, 16),
+                           max_tree_depth=7, flags=_abi.FLAG_ACCUM_WELFORD)
+    g = GpuBackend("fast")
+    monkeypatch.delenv("MCMC_NUTS_CHUNK", raising=False)
+    ref = g.run(_abi.SAMPLER_NUTS, p, q0, welford=wf)
+    o = oracle.run(_abi.SAMPLER_NUTS, p, q0, welford=wf)
+    assert np.array_equal(ref["tree_depths"], o["tree_depths"])
+    for j in range(4):
+        assert int(ref["counters"][j]) == int(o["counters"][j]), j
+    for ci in ("1", "4"):
+        monkeypatch.setenv("MCMC_NUTS_CHUNK", ci)
+        got = g.run(_abi.SAMPLER_NUTS, p, q0, welford=wf)
+        for k in ref:
+            assert np.array_equal(ref[k], got[k], equal_nan=True), (ci, k)
+
+
 @pytest.mark.parametrize("name,sampler,sched,D", [("rosenbrock", _abi.SAMPLER_HMC, None, 20),
                                                   ("neals_funnel", _abi.SAMPLER_GRAHMC, "tanh", 20),
                                                   ("standard_normal", _abi.SAMPLER_GRAHMC, "constant", 10),
