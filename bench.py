@@ -41,6 +41,11 @@ STEP_SIZE = 0.02         # fixed epsilon, see DESIGN.md (short dual-averaging ru
 INV_MASS = np.linspace(0.5, 2.0, D)  # a non-trivial diagonal M^-1 to exercise the path
 SEED = (0, 0)
 # algorithmic fp64 flops of THIS kernel's formulation (FMA = 2), DESIGN.md "flop model"
+# dram__bytes_read.sum + dram__bytes_write.sum of one hmc_kernel launch at the bench shape (ncu --set full captures of
+# L=16 and L=128: 802.3 MB and 778.6 MB, profiles/ncu_hmc_L{16,128}_r01c.txt) — a constant from the profile, not a live
+# measurement; the algorithmic bytes are the stored samples + log-probs, the initial state read and the final q / g written
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 790.4e6
+NCU_TRAFFIC_SOURCE = "profiles/ncu_hmc_L16_r01c.txt, profiles/ncu_hmc_L128_r01c.txt (mean of the two launches)"
 F_STEP = 231.0           # per leapfrog step of one 20-D rosenbrock chain: 80 integrator (2 DFMA/dim) + 151 gradient (75 DFMA + 1 DMUL)
 F_ITER = 190.0           # per MH iteration outside the trajectory (momentum scaling, two kinetic energies, value)
 
@@ -329,7 +334,8 @@ def run_gpu_arm(args) -> None:
             "per_L": {str(L): {"ms_per_call": kern_ms[L] / args.steps,
                                "grad_evals_per_sec": C * S_STORED * L * args.steps / (kern_ms[L] * 1e-3)} for L in L_GRID},
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                         "traffic": None,
+                         "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH, "traffic_source": NCU_TRAFFIC_SOURCE,
+                         "algorithmic_bytes_per_launch": wb_bytes + 3 * C * D * 8 + 2 * C * 8,
                          "kernel": "mcmc::hmc_kernel<6, 20, false, 64> (rosenbrock, D=20, HMC)",
                          "peak_source": "mcmc_fp64_peak_probe measured in this run (register-resident DFMA, all SMs); "
                                         "MEASURED_PEAKS.json has no fp64 entry; nominal 37.2 TFLOP/s",

@@ -21,7 +21,7 @@ for L in 16 128; do
       python tools/perf_hmc.py --samples 64 --Ls $L --eps 0.02 > $O/ncu_hmc_L${L}_$TAG.log 2>&1 || echo "hmc L=$L capture failed" >&2
 done
 step $NCU_FULL -k regex:nuts_kernel -s 1 -c 1 -f -o $O/nuts_rb_$TAG \
-    python tools/perf_hmc.py --sampler nuts --samples 32 --Ls 1 --eps 0.02 > $O/ncu_nuts_$TAG.log 2>&1 || echo "nuts capture failed" >&2
+    python tools/perf_hmc.py --sampler nuts --samples 96 --Ls 1 --eps 0.02 > $O/ncu_nuts_$TAG.log 2>&1 || echo "nuts capture failed" >&2
 step $NCU_FULL -k regex:rwmh_kernel -s 1 -c 1 -f -o $O/rwmh_$TAG \
     python tools/perf_hmc.py --sampler rwmh --target standard_normal --chains 1048576 --samples 64 --Ls 1 --eps 0.5 \
     > $O/ncu_rwmh_$TAG.log 2>&1 || echo "rwmh capture failed" >&2
