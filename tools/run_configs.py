@@ -99,6 +99,9 @@ def config3(chains_total, schedules, friction):
     off, C = shard(chains_total)
     tgt = T.neals_funnel(D)
     q0 = torch.from_numpy(tgt.init_sampler(split(3, 1 + dist.world_size())[dist.rank()], C)).cuda()
+    # untimed pass with the same shapes: module load, torch's caching allocator, NCCL communicator warm-up
+    run_adaptive_warmup("grahmc", tgt.log_prob_fn, None, q0, key=11, num_warmup=300, schedule_type=schedules[0],
+                        num_steps=16, chain_offset=off, verbose=False, tune_friction=False)
     for sch in schedules:
         with Timer() as tm:
             eps, w, pos, info = run_adaptive_warmup("grahmc", tgt.log_prob_fn, None, q0, key=11, num_warmup=2500,
