@@ -83,7 +83,7 @@ def config2(chains_total):
     w = torch.linspace(0.5, 2.0, D, dtype=torch.float64, device="cuda")
     for L in (16, 32, 64, 128):
         # same shapes as the timed call, so the 2.7 GB sample buffer comes from torch's cache, not cudaMalloc
-        hmc_run(5, tgt.log_prob_fn, q0, 0.02, L, 256, burn_in=0, inv_mass_matrix=w, _chain_offset=off)
+        hmc_run(5, tgt.log_prob_fn, q0, 0.02, L, 256, burn_in=64, inv_mass_matrix=w, _chain_offset=off)
         with Timer() as tm:
             smp, lps, acc, st = hmc_run(7, tgt.log_prob_fn, q0, 0.02, L, 256, burn_in=64, inv_mass_matrix=w,
                                         _chain_offset=off)
