@@ -1,0 +1,112 @@
+"""Generates tests/golden/reference_host_golden.npz: outputs of the reference's own HOST-SIDE source on seeded inputs —
+dual averaging (tuning/dual_averaging.py da_* and joint_da_*), Welford (tuning/welford.py), the warmup schedule
+(tuning/adaptation.py build_schedule), the five friction schedules (samplers/GRAHMC.py:69-106), and every
+benchmarks/targets.py factory: true_mean / true_cov, log-density and autodiff gradient at random points for default and
+non-default parameters.  Same mechanism as make_reference_golden.py (the reference's files imported unmodified from
+/root/reference on the torch-fp64 stand-in for jax).  Build container only."""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+import make_reference_golden as G  # noqa: E402  (sets up the stand-in and loads samplers / targets)
+
+sys.path.insert(0, G.REF)          # tuning/*.py import `samplers.X` / `tuning.Y` as packages
+import jax  # noqa: E402
+import jax.numpy as jnp  # noqa: E402
+import torch  # noqa: E402
+from tuning import adaptation as A, dual_averaging as DA, welford as W  # noqa: E402
+
+np64 = G.np64
+blob = {}
+
+# ---- dual averaging: 45 updates with two window resets (adaptation.py:164-165 pattern)
+rng = np.random.default_rng(5)
+for tag, eps0, target in (("da_hmc", 0.1, 0.65), ("da_nuts", 0.5, 0.8), ("da_rwmh", 2.38 / np.sqrt(20), 0.234)):
+    acc = np.clip(target + 0.25 * rng.standard_normal(45), 0.0, 1.0)
+    st = DA.da_init(eps0)
+    rows = [[st.log_step, st.log_step_bar, st.H_bar, st.mu, st.count]]
+    for i, a in enumerate(acc):
+        if i in (12, 30):
+            st = DA.da_reset(st)
+            rows.append([st.log_step, st.log_step_bar, st.H_bar, st.mu, st.count])
+        st = DA.da_update(st, float(a), target)
+        rows.append([st.log_step, st.log_step_bar, st.H_bar, st.mu, st.count])
+    blob[f"{tag}|accept"] = acc
+    blob[f"{tag}|init"] = np.array([eps0, target])
+    blob[f"{tag}|states"] = np.array(rows, dtype=np.float64)
+acc = np.clip(0.65 + 0.3 * rng.standard_normal(40), 0.0, 1.0)
+st = DA.joint_da_init(jnp.array([0.1, 1.0]))
+rows = []
+for a in acc:
+    st = DA.joint_da_update(st, float(a), 0.65)
+    rows.append(np.concatenate([np64(st.log_params), np64(st.log_params_bar), [st.H_bar, st.count]]))
+blob["joint_da|accept"] = acc
+blob["joint_da|states"] = np.array(rows)
+
+# ---- Welford
+x = rng.standard_normal((60, 7)) * np.linspace(0.1, 5.0, 7) + np.arange(7)
+st = W.welford_init(7)
+for row in x[:20]:
+    st = W.welford_update(st, jnp.asarray(row))
+blob["welford|x"] = x
+blob["welford|after20"] = np.stack([np64(st.mean), np64(st.m2)])
+st = W.welford_update_batch(st, jnp.asarray(x[20:]))
+mean, var = W.welford_covariance(st)
+blob["welford|final"] = np.stack([np64(st.mean), np64(st.m2), np64(mean), np64(var)])
+blob["welford|count"] = np64(st.count)
+m1, v1 = W.welford_covariance(W.welford_update(W.welford_init(7), jnp.asarray(x[0])))   # n clamps to 2
+blob["welford|one_sample_var"] = np64(v1)
+
+# ---- warmup schedule
+for tag, kw in (("default", {}), ("short", dict(exploration_steps=100, adaptation_windows=[25, 50], cooldown_steps=25))):
+    s = A.build_schedule(**kw)
+    blob[f"schedule|{tag}"] = np.array([[a, b, {"exploration": 0, "adaptation": 1, "cooldown": 2}[p]] for a, b, p in s])
+
+# ---- friction schedules gamma(t) (GRAHMC.py:69-106): t = i*eps, T = eps*L
+for name in ("constant", "tanh", "sigmoid", "linear", "sine"):
+    f = G.GRAHMC.get_friction_schedule(name)
+    for L, eps, gam, steep in ((16, 0.05, 1.0, 0.5), (7, 0.3, 2.5, 2.0), (128, 0.01, 0.3, 5.0)):
+        T_ = eps * L
+        blob[f"friction|{name}|{L}|{eps}|{gam}|{steep}"] = np.array(
+            [float(f(jnp.asarray(i * eps), jnp.asarray(T_), gam, steep)) for i in range(L)])
+
+# ---- targets: metadata, value and autodiff gradient
+TARGET_PARAMS = {
+    "standard_normal": [{}],
+    "correlated_gaussian": [dict(correlation=0.9), dict(correlation=0.3)],
+    "ill_conditioned_gaussian": [dict(condition_number=100.0), dict(condition_number=1e4)],
+    "neals_funnel": [{}],
+    "log_gamma": [dict(shape=2.0, rate=1.0), dict(shape=3.5, rate=0.5)],
+    "student_t": [dict(df=3.0), dict(df=7.5)],
+    "rosenbrock": [dict(scale=0.1), dict(scale=0.02)],
+    "gaussian_mixture": [dict(n_modes=2, separation=5.0), dict(n_modes=2, separation=2.0)],
+}
+vg = jax.vmap(jax.value_and_grad(lambda x: x.sum()))  # placeholder to warm the stand-in
+names = []
+for name, plist in TARGET_PARAMS.items():
+    for kw in plist:
+        for D in (10, 20, 7) if name != "rosenbrock" else (10, 20, 6):
+            t = getattr(G.T, name)(dim=D, **kw)
+            if name == "log_gamma":
+                pts = 0.2 + np.abs(rng.standard_normal((12, D))) * 1.5
+            else:
+                pts = rng.standard_normal((12, D)) * (2.0 if name == "student_t" else 1.0)
+            lp, g = jax.vmap(jax.value_and_grad(t.log_prob_fn))(jnp.asarray(pts))
+            key = f"target|{name}|{D}|{repr(sorted(kw.items()))}"
+            names.append(key)
+            blob[key + "|x"] = pts
+            blob[key + "|lp"] = np64(lp)
+            blob[key + "|grad"] = np64(g)
+            blob[key + "|true_mean"] = np64(t.true_mean) if t.true_mean is not None else np.zeros(0)
+            blob[key + "|true_cov"] = np64(t.true_cov) if t.true_cov is not None else np.zeros(0)
+blob["target_keys"] = np.array(names)
+# known-answer facts of SURVEY.md 8c, from the reference's own functions
+blob["kat|rosenbrock_at_ones"] = np64(G.T.rosenbrock(dim=20).log_prob_fn(jnp.ones(20)))
+blob["kat|standard_normal_at_zero"] = np64(G.T.standard_normal(dim=20).log_prob_fn(jnp.zeros(20)))
+
+path = os.path.join(HERE, "reference_host_golden.npz")
+np.savez_compressed(path, **blob)
+print("wrote", path, os.path.getsize(path), "bytes;", len(names), "target cases")
