@@ -30,8 +30,9 @@ def _dev(x) -> torch.Tensor:
 
 
 def sliced_wasserstein_distance(samples1, samples2, n_projections: int = 500, key=None,
-                                projection_batch_size: int = 100) -> float:
-    """metrics.py:12-84."""
+                                projection_batch_size: int = 100, directions=None) -> float:
+    """metrics.py:12-84.  `directions` (n_projections, dim), unnormalised, replaces the drawn projection directions
+    (the hook the parity test uses to feed the reference run's own directions)."""
     if key is None:
         key = PRNGKey(30)
     s1, s2 = _dev(samples1), _dev(samples2)
@@ -42,7 +43,10 @@ def sliced_wasserstein_distance(samples1, samples2, n_projections: int = 500, ke
     w2 = []
     for b in range(n_batches):
         cur = min((b + 1) * projection_batch_size, n_projections) - b * projection_batch_size
-        dirs = normal(fold_in(key, b), (cur, dim))
+        if directions is not None:
+            dirs = np.asarray(directions, dtype=np.float64)[b * projection_batch_size:b * projection_batch_size + cur]
+        else:
+            dirs = normal(fold_in(key, b), (cur, dim))
         dirs = dirs / np.linalg.norm(dirs, axis=1, keepdims=True)
         dt = torch.from_numpy(dirs).to(s1.device)
         p1 = torch.sort(s1 @ dt.T, dim=0).values

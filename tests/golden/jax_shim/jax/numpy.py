@@ -80,8 +80,12 @@ def where(c, a, b): return _torch.where(_t(c), *_pair(a, b))
 def clip(x, a_min=None, a_max=None): return _torch.clamp(_t(x), min=a_min, max=a_max)
 
 
+def sort(x, axis=-1): return _torch.sort(_t(x), dim=axis).values
+def quantile(x, q, axis=None): return _torch.quantile(_t(x), _t(q, _torch.float64), dim=axis, interpolation="linear")
+
+
 class linalg:
     cholesky = staticmethod(lambda a: _torch.linalg.cholesky(_t(a)))
     inv = staticmethod(lambda a: _torch.linalg.inv(_t(a)))
     solve = staticmethod(lambda a, b: _torch.linalg.solve(_t(a), _t(b)))
-    norm = staticmethod(lambda a, **k: _torch.linalg.norm(_t(a)))
+    norm = staticmethod(lambda a, axis=None, keepdims=False: _torch.linalg.norm(_t(a), dim=axis, keepdim=keepdims))

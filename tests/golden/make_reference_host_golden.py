@@ -107,6 +107,39 @@ blob["target_keys"] = np.array(names)
 blob["kat|rosenbrock_at_ones"] = np64(G.T.rosenbrock(dim=20).log_prob_fn(jnp.ones(20)))
 blob["kat|standard_normal_at_zero"] = np64(G.T.standard_normal(dim=20).log_prob_fn(jnp.zeros(20)))
 
+# ---- Sliced Wasserstein-2 (benchmarks/metrics.py:12-84) with the projection directions recorded
+from benchmarks import metrics as M  # noqa: E402
+from jax._core import DRAW_LOG  # noqa: E402
+s1 = rng.standard_normal((300, 5)) * np.array([1.0, 2.0, 0.5, 1.0, 3.0])
+s2 = rng.standard_normal((300, 5)) + 0.3
+s3 = rng.standard_normal((200, 5)) * 1.5
+for tag, a, b in (("equal", s1, s2), ("unequal", s1, s3)):
+    del DRAW_LOG[:]
+    val = M.sliced_wasserstein_distance(jnp.asarray(a), jnp.asarray(b), n_projections=30, projection_batch_size=16)
+    blob[f"sw2|{tag}|a"], blob[f"sw2|{tag}|b"] = a, b
+    blob[f"sw2|{tag}|directions"] = np.concatenate([v.reshape(-1, 5) for k, _, v in DRAW_LOG if k == "normal"])
+    blob[f"sw2|{tag}|value"] = np.float64(val)
+
+# ---- Bonferroni z-test gate and gate constants (run_benchmarks.py:55-62,90-158); arviz is only imported there, stubbed
+import types  # noqa: E402
+import pandas as pd  # noqa: E402
+sys.modules.setdefault("arviz", types.ModuleType("arviz"))
+RB = G.load("run_benchmarks.py", "ref_run_benchmarks")
+for name in ("MIN_ESS_HARD_GATE", "MIN_ESS_TAIL_HARD_GATE", "MIN_ESS_QUALITY", "MIN_ESS_TAIL_QUALITY", "INEFFICIENT_THRESHOLD",
+             "HIGH_EFFICIENCY_THRESHOLD"):
+    blob[f"gate_const|{name}"] = np.float64(getattr(RB, name))
+for tag, D, shift in (("pass", 20, 1.0), ("fail", 20, 4.5), ("d10", 10, 2.9)):
+    tgt = G.T.ill_conditioned_gaussian(dim=D)
+    mcse = 0.01 + 0.02 * rng.random(D)
+    means = np64(tgt.true_mean) + shift * mcse * np.sign(rng.standard_normal(D)) * rng.random(D)
+    r = RB.check_summary_statistics({"summary": pd.DataFrame({"mean": means, "mcse_mean": mcse})}, tgt)
+    blob[f"ztest|{tag}|means"], blob[f"ztest|{tag}|mcse"] = means, mcse
+    blob[f"ztest|{tag}|out"] = np.array([float(r["pass"]), r["max_z"], r["threshold"]])
+    blob[f"ztest|{tag}|z"] = np.asarray(r["z_scores"], dtype=np.float64)
+dh = np.array([0.0, 999.9, -1000.1, 1e4, -3.0, np.inf])
+blob["divergences|dh"] = dh
+blob["divergences|flags"] = np64(RB.detect_divergences(jnp.asarray(dh))).astype(np.int8)
+
 path = os.path.join(HERE, "reference_host_golden.npz")
 np.savez_compressed(path, **blob)
 print("wrote", path, os.path.getsize(path), "bytes;", len(names), "target cases")

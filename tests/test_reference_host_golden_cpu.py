@@ -111,3 +111,23 @@ def test_oracle_target_value_and_gradient_match_reference_autodiff(oracle, key):
 def test_known_answers_from_reference_source():
     assert float(BLOB["kat|rosenbrock_at_ones"].ravel()[0]) == 0.0
     assert abs(float(BLOB["kat|standard_normal_at_zero"].ravel()[0]) + 10.0 * np.log(2.0 * np.pi)) < 1e-13
+
+
+@pytest.mark.parametrize("tag,D", [("pass", 20), ("fail", 20), ("d10", 10)])
+def test_z_test_gate_matches_reference_source(tag, D):
+    """run_benchmarks.py:108-158 (Bonferroni threshold from scipy's norm.ppf there, restated here)."""
+    from mcmc_b200 import diagnostics as DG
+    tgt = T.ill_conditioned_gaussian(dim=D)
+    r = DG.check_summary_statistics({"summary": {"mean": BLOB[f"ztest|{tag}|means"], "mcse_mean": BLOB[f"ztest|{tag}|mcse"]}}, tgt)
+    want = BLOB[f"ztest|{tag}|out"]
+    assert float(r["pass"]) == want[0]
+    assert abs(r["max_z"] - want[1]) <= 1e-12 * max(1.0, want[1])
+    assert abs(r["threshold"] - want[2]) <= 1e-9
+    assert relerr(r["z_scores"], BLOB[f"ztest|{tag}|z"]) <= 1e-12
+
+
+def test_gate_constants_match_reference_source():
+    from mcmc_b200 import diagnostics as DG
+    for k in BLOB.files:
+        if k.startswith("gate_const|"):
+            assert float(getattr(DG, k.split("|")[1])) == float(BLOB[k].ravel()[0]), k

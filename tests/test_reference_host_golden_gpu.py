@@ -32,3 +32,19 @@ def test_cuda_friction_table_matches_reference_source(gpu_lib, key, variant):
     want = BLOB[key]
     assert relerr(g.cpu().numpy(), want) <= 1e-14
     assert relerr(s.cpu().numpy(), np.exp(-want * (0.5 * float(eps)))) <= 1e-14
+
+
+@pytest.mark.parametrize("tag", ["equal", "unequal"])
+def test_sliced_w2_matches_reference_source(gpu_lib, tag):
+    """benchmarks/metrics.py:12-84 with the reference run's own projection directions (equal counts: sorted RMS;
+    unequal: linear-interpolation quantiles)."""
+    from mcmc_b200.benchmarks.metrics import sliced_wasserstein_distance
+    got = sliced_wasserstein_distance(BLOB[f"sw2|{tag}|a"], BLOB[f"sw2|{tag}|b"], n_projections=30, projection_batch_size=16,
+                                      directions=BLOB[f"sw2|{tag}|directions"])
+    assert abs(got - float(BLOB[f"sw2|{tag}|value"].ravel()[0])) <= 1e-12
+
+
+def test_detect_divergences_matches_reference_source(gpu_lib):
+    from mcmc_b200.diagnostics import detect_divergences
+    got = detect_divergences(torch.from_numpy(BLOB["divergences|dh"]).cuda())
+    assert np.array_equal(got.cpu().numpy().astype(np.int8), BLOB["divergences|flags"])
