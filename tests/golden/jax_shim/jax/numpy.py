@@ -58,7 +58,9 @@ def _red(fn, x, axis, keepdims=False):
 
 
 def sum(x, axis=None, keepdims=False): return _red(_torch.sum, x, axis, keepdims)
-def mean(x, axis=None, keepdims=False): return _red(_torch.mean, x, axis, keepdims)
+def mean(x, axis=None, keepdims=False):
+    x = _t(x)
+    return _red(_torch.mean, x if x.is_floating_point() else x.to(_torch.float64), axis, keepdims)
 def max(x, axis=None): return _red(_torch.amax, x, axis) if axis is not None else _torch.max(_t(x))
 def min(x, axis=None): return _red(_torch.amin, x, axis) if axis is not None else _torch.min(_t(x))
 def all(x, axis=None): return _torch.all(_t(x)) if axis is None else _torch.all(_t(x), dim=axis)

@@ -140,6 +140,89 @@ dh = np.array([0.0, 999.9, -1000.1, 1e4, -3.0, np.inf])
 blob["divergences|dh"] = dh
 blob["divergences|flags"] = np64(RB.detect_divergences(jnp.asarray(dh))).astype(np.int8)
 
+# ---- run_adaptive_warmup control flow (tuning/adaptation.py:72-348) with the sampler replaced by warmup_mock.mock_batch
+import collections  # noqa: E402
+import contextlib  # noqa: E402
+import io  # noqa: E402
+from warmup_mock import mock_batch  # noqa: E402
+_State = collections.namedtuple("_State", "position")
+for tag, sampler, kw in (("hmc", "hmc", {}), ("nuts", "nuts", {}), ("hmc_identity", "hmc", dict(learn_mass_matrix=False))):
+    calls = [0]
+    steps = []
+
+    def fake_run(key, f, position, step_size, *a, num_samples=None, inv_mass_matrix=None, **k):
+        smp, cnt = mock_batch(calls[0], np64(position), step_size, None if inv_mass_matrix is None else np64(inv_mass_matrix),
+                              num_samples)
+        calls[0] += 1
+        steps.append(float(step_size))
+        rate = jnp.asarray(cnt).astype(jnp.float32) / num_samples      # HMC.py:313: float32 count / num_samples
+        st = _State(position=jnp.asarray(smp[-1]))
+        if sampler == "nuts":                                            # (samples, lps, rate, state, depths, mean_accept_probs)
+            return jnp.asarray(smp), None, rate, st, None, jnp.asarray(np.broadcast_to(np64(rate.to(jnp.float64)), smp.shape[:2]).copy())
+        return jnp.asarray(smp), None, rate, st
+
+    A.hmc_run, A.nuts_run = fake_run, fake_run
+    C_, D_ = 4, 6
+    q0 = rng.standard_normal((C_, D_))
+    with contextlib.redirect_stdout(io.StringIO()):
+        eps, w, pos, info = A.run_adaptive_warmup(sampler, None, None, jnp.asarray(q0), jax.random.PRNGKey(1), num_warmup=2500,
+                                                  target_accept=0.65, **kw)
+    blob[f"warmup|{tag}|q0"] = q0
+    blob[f"warmup|{tag}|step_sizes"] = np.array(steps)
+    blob[f"warmup|{tag}|final_step"] = np.float64(eps)
+    blob[f"warmup|{tag}|inv_mass"] = np64(w) if w is not None else np.zeros(0)
+    blob[f"warmup|{tag}|position"] = np64(pos)
+
+# ---- the convergence loops of dual_averaging_tune_{rwmh,hmc,nuts} (dual_averaging.py:16-382), same mock sampler
+for tag in ("rwmh", "hmc", "nuts"):
+    calls = [0]
+
+    def fake(key, f, position, *a, num_samples=None, step_size=None, scale=None, **k):
+        v = scale if tag == "rwmh" else step_size
+        smp, cnt = mock_batch(calls[0], np64(position), v * (0.25 if tag == "rwmh" else 1.0), None, num_samples)
+        calls[0] += 1
+        rate = jnp.asarray(cnt).astype(jnp.float32) / num_samples
+        st = _State(position=jnp.asarray(smp[-1]))
+        if tag == "nuts":
+            depths = jnp.asarray(np.full(smp.shape[:2], 3 + calls[0] % 2, dtype=np.int32))
+            return None, None, rate, st, depths, jnp.asarray(np.broadcast_to(np64(rate.to(jnp.float64)), smp.shape[:2]).copy())
+        return None, None, rate, st
+
+    DA.rwMH_run = DA.hmc_run = DA.nuts_run = fake
+    q0 = rng.standard_normal((4, 6))
+    with contextlib.redirect_stdout(io.StringIO()):
+        if tag == "rwmh":
+            v, h = DA.dual_averaging_tune_rwmh(jax.random.PRNGKey(2), None, jnp.asarray(q0), max_iter=400)
+        elif tag == "hmc":
+            v, h = DA.dual_averaging_tune_hmc(jax.random.PRNGKey(2), None, jnp.asarray(q0), 8, max_iter=400)
+        else:
+            v, h = DA.dual_averaging_tune_nuts(jax.random.PRNGKey(2), None, jnp.asarray(q0), max_iter=400)
+    blob[f"tuner|{tag}|q0"] = q0
+    blob[f"tuner|{tag}|value"] = np.float64(v)
+    blob[f"tuner|{tag}|history"] = np.array(h["scale_history" if tag == "rwmh" else "step_size_history"], dtype=np.float64)
+    blob[f"tuner|{tag}|accept"] = np.array(h["accept_history"], dtype=np.float64)
+    blob[f"tuner|{tag}|converged_iter"] = np.int64(h["converged_iter"])
+    if tag == "nuts":
+        blob[f"tuner|{tag}|depth"] = np.array(h["tree_depth_history"], dtype=np.float64)
+
+# ---- joint (step size, gamma) tuning loop (dual_averaging.py:668-804); the mock's accept rate falls with step * (1 + gamma/4)
+calls = [0]
+
+
+def fake_rahmc(key, f, position, *a, num_samples=None, step_size=None, gamma=None, **k):
+    smp, cnt = mock_batch(calls[0], np64(position), step_size * (1.0 + 0.25 * gamma), None, num_samples)
+    calls[0] += 1
+    return None, None, jnp.asarray(cnt).astype(jnp.float32) / num_samples, _State(position=jnp.asarray(smp[-1]))
+
+
+DA.rahmc_run = fake_rahmc
+q0 = rng.standard_normal((4, 6))
+with contextlib.redirect_stdout(io.StringIO()):
+    st_, gm_, sp_, h = DA.joint_tune_grahmc(jax.random.PRNGKey(3), None, None, jnp.asarray(q0), 8, schedule_type="tanh", max_iter=120)
+blob["joint_tuner|q0"] = q0
+blob["joint_tuner|final"] = np.array([st_, gm_, sp_])
+blob["joint_tuner|history"] = np.array([h["step_size"], h["gamma"], h["accept_rate"]], dtype=np.float64)
+
 path = os.path.join(HERE, "reference_host_golden.npz")
 np.savez_compressed(path, **blob)
 print("wrote", path, os.path.getsize(path), "bytes;", len(names), "target cases")

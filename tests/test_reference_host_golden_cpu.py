@@ -131,3 +131,108 @@ def test_gate_constants_match_reference_source():
     for k in BLOB.files:
         if k.startswith("gate_const|"):
             assert float(getattr(DG, k.split("|")[1])) == float(BLOB[k].ravel()[0]), k
+
+
+@pytest.mark.parametrize("tag,sampler,kw", [("hmc", "hmc", {}), ("nuts", "nuts", {}), ("hmc_identity", "hmc", dict(learn_mass_matrix=False))])
+def test_warmup_control_flow_matches_reference_source(monkeypatch, oracle, tag, sampler, kw):
+    """run_adaptive_warmup with the sampler replaced by the same deterministic function on both sides
+    (tests/golden/warmup_mock.py): 26 dual-averaging updates at the same step sizes, the same learned metric.
+    The reference averages float32 accept rates (HMC.py:313, adaptation.py:218); here the integer counts are summed
+    exactly, so step sizes agree to float32 rounding (1e-6) and the metric, which does not depend on them, to 1e-12."""
+    import torch
+    from golden.warmup_mock import mock_batch
+    from helpers import oracle_welford_sum_var
+    calls, steps = [0], []
+
+    def fake_sample_batch(sid, log_prob_fn, position, key, num_samples, *, step_size, inv_mass_matrix=None, welford=None,
+                          welford_count=0.0, **_k):
+        pos = position.numpy()
+        smp, cnt = mock_batch(calls[0], pos, step_size, None if inv_mass_matrix is None else inv_mass_matrix.numpy(), num_samples)
+        calls[0] += 1
+        steps.append(float(step_size))
+        if welford is not None:   # what the kernels do under MCMC_FLAG_ACCUM_WELFORD: one fold per stored draw and chain
+            mean, m2 = welford[0].numpy(), welford[1].numpy()
+            n = float(welford_count)
+            for x in smp:
+                n += 1.0
+                delta = x - mean
+                mean += delta / n
+                m2 += delta * (x - mean)
+        out = {"final_q": torch.from_numpy(smp[-1].copy()), "counters": torch.tensor([int(cnt.sum()), 0, 0, 0])}
+        if sid == _abi.SAMPLER_NUTS:   # adaptation.py:187: the statistic is the mean accept probability of the trajectories
+            rate = (cnt.astype(np.float32) / np.float32(num_samples)).astype(np.float64)
+            out["accept_sum"] = torch.tensor(float(rate.sum() * num_samples))
+        else:
+            out["accept_sum"] = torch.tensor(float(cnt.sum()))
+        out["accept_terms"] = len(cnt) * int(num_samples)
+        return out
+
+    monkeypatch.setattr(A, "sample_batch", fake_sample_batch)
+    monkeypatch.setattr(A, "welford_sum_var", oracle_welford_sum_var)
+    monkeypatch.setattr(A, "_as_state_tensor", lambda x: torch.as_tensor(np.asarray(x), dtype=torch.float64).contiguous()
+                        if not isinstance(x, torch.Tensor) else x.to(torch.float64).contiguous())
+    eps, w, pos, info = A.run_adaptive_warmup(sampler, None, None, BLOB[f"warmup|{tag}|q0"], 1, num_warmup=2500, target_accept=0.65,
+                                              verbose=False, **kw)
+    want_steps = BLOB[f"warmup|{tag}|step_sizes"]
+    assert len(steps) == len(want_steps) == 26 and info["num_da_updates"] == 26
+    assert relerr(np.array(steps), want_steps) <= 2e-6
+    assert abs(eps - float(BLOB[f"warmup|{tag}|final_step"].ravel()[0])) <= 2e-6 * eps
+    assert relerr(w.numpy(), BLOB[f"warmup|{tag}|inv_mass"]) <= 1e-12
+    assert relerr(pos.numpy(), BLOB[f"warmup|{tag}|position"]) <= 1e-12
+
+
+@pytest.mark.parametrize("tag", ["rwmh", "hmc", "nuts"])
+def test_tuner_convergence_loops_match_reference_source(monkeypatch, tag):
+    """dual_averaging_tune_{rwmh,hmc,nuts} (dual_averaging.py:16-382) with the same mock sampler on both sides: same
+    iteration of convergence, same histories (to the float32 rounding of the reference's accept rates)."""
+    import torch
+    from golden.warmup_mock import mock_batch
+    calls = [0]
+
+    def fake_sample_batch(sid, log_prob_fn, position, key, num_samples, *, step_size, **_k):
+        pos = position.numpy() if isinstance(position, torch.Tensor) else np.asarray(position)
+        smp, cnt = mock_batch(calls[0], pos, step_size * (0.25 if tag == "rwmh" else 1.0), None, num_samples)
+        calls[0] += 1
+        rate = (cnt.astype(np.float32) / np.float32(num_samples)).astype(np.float64)
+        depth = 3 + calls[0] % 2
+        return {"final_q": torch.from_numpy(smp[-1].copy()), "accept_terms": len(cnt) * int(num_samples),
+                "accept_sum": torch.tensor(float(rate.sum() * num_samples) if tag == "nuts" else float(cnt.sum())),
+                "counters": torch.tensor([int(cnt.sum()), 0, depth * len(cnt) * int(num_samples), 0])}
+
+    monkeypatch.setattr(DA, "sample_batch", fake_sample_batch)
+    q0 = torch.from_numpy(BLOB[f"tuner|{tag}|q0"])
+    if tag == "rwmh":
+        v, h = DA.dual_averaging_tune_rwmh(2, None, q0, max_iter=400)
+        hist = h["scale_history"]
+    elif tag == "hmc":
+        v, h = DA.dual_averaging_tune_hmc(2, None, q0, 8, max_iter=400)
+        hist = h["step_size_history"]
+    else:
+        v, h = DA.dual_averaging_tune_nuts(2, None, q0, max_iter=400)
+        hist = h["step_size_history"]
+        assert relerr(np.array(h["tree_depth_history"]), BLOB[f"tuner|{tag}|depth"]) <= 1e-12
+    assert h["converged_iter"] == int(BLOB[f"tuner|{tag}|converged_iter"].ravel()[0])
+    assert len(hist) == len(BLOB[f"tuner|{tag}|history"])
+    assert relerr(np.array(hist), BLOB[f"tuner|{tag}|history"]) <= 5e-6
+    assert relerr(np.array(h["accept_history"]), BLOB[f"tuner|{tag}|accept"]) <= 1e-6
+    assert abs(v - float(BLOB[f"tuner|{tag}|value"].ravel()[0])) <= 5e-6 * v
+
+
+def test_joint_tuner_matches_reference_source(monkeypatch):
+    """joint_tune_grahmc (dual_averaging.py:668-804) with the same mock sampler on both sides."""
+    import torch
+    from golden.warmup_mock import mock_batch
+    calls = [0]
+
+    def fake_sample_batch(sid, log_prob_fn, position, key, num_samples, *, step_size, gamma, **_k):
+        pos = position.numpy() if isinstance(position, torch.Tensor) else np.asarray(position)
+        smp, cnt = mock_batch(calls[0], pos, step_size * (1.0 + 0.25 * gamma), None, num_samples)
+        calls[0] += 1
+        return {"final_q": torch.from_numpy(smp[-1].copy()), "accept_terms": len(cnt) * int(num_samples),
+                "accept_sum": torch.tensor(float(cnt.sum())), "counters": torch.tensor([int(cnt.sum()), 0, 0, 0])}
+
+    monkeypatch.setattr(DA, "sample_batch", fake_sample_batch)
+    st, gm, sp, h = DA.joint_tune_grahmc(3, None, None, torch.from_numpy(BLOB["joint_tuner|q0"]), 8, schedule_type="tanh", max_iter=120)
+    want = BLOB["joint_tuner|final"]
+    assert abs(st - want[0]) <= 5e-6 * want[0] and abs(gm - want[1]) <= 5e-6 * want[1] and sp == want[2]
+    assert relerr(np.array([h["step_size"], h["gamma"], h["accept_rate"]]), BLOB["joint_tuner|history"]) <= 5e-6
