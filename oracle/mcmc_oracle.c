@@ -5,12 +5,20 @@
  * cpu_baseline / --impl reference legs may load this; the product path
  * (mcmc_b200/) never does.
  *
- * PARITY UNPINNED: the reference ships no tests, golden vectors or fixtures
- *  and needs jax==0.8.0, which is not installable here (F3), so
- * this restatement cannot be checked against outputs of the reference itself.
- * It is pinned instead on (a) known-answer facts derived from the source
- * (SURVEY.md §8c), (b) an independent NumPy restatement (oracle/oracle_np.py)
- * and (c) torch fp64 autograd of each log-density as coded, for the gradients.
+ * PARITY: pinned against the reference's own SOURCE, not against jax itself.  The
+ * reference ships no tests, golden vectors or fixtures and needs
+ * jax==0.8.0, which is not installable here (F3).  tests/golden/make_reference_golden.py
+ * therefore imports the reference's files unmodified from /root/reference on top of
+ * a torch-fp64 stand-in for the jax API (tests/golden/jax_shim: eager IEEE double
+ * arithmetic in source order, vmap = loop, value_and_grad = autograd) and records
+ * inputs, draws and outputs of 24 hmc/grahmc/rwmh/nuts runs in
+ * tests/golden/reference_golden.npz; this restatement reproduces them within 5e-13
+ * relative with identical accept counts and tree depths (tests/test_reference_golden_cpu.py).
+ * NOT pinned: XLA's own exp/log/tanh roundings and jax's threefry streams
+ * ("parity unpinned" in that narrower sense).  Also pinned on (a) known-answer
+ * facts derived from the source, (b) an independent NumPy
+ * restatement (oracle/oracle_np.py) and (c) torch fp64 autograd of each log-density
+ * as coded, for the gradients.
  *
  * It follows the reference operation by operation (compile with
  * -ffp-contract=off so no FMA is formed, as in the reference's jnp expressions):

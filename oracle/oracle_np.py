@@ -5,8 +5,9 @@ oracle (oracle/mcmc_oracle.c): both are written from the reference source, in
 different languages and loop orders (this one is vectorised over chains like
 the reference's vmap; the C one is chain-outer), and must agree to rounding.
 
-PARITY UNPINNED (see the header of mcmc_oracle.c): the reference has no tests
-or golden vectors and jax is not installable here.
+PARITY (see the header of mcmc_oracle.c): pinned against the reference's own source run on a
+torch-fp64 stand-in for jax (tests/golden/reference_golden.npz, tests/test_reference_golden_cpu.py);
+jax/XLA numerics and threefry themselves stay unpinned (jax is not installable here).
 
 Follows, with injected randomness (z: (iters, C, D) normals, u: (iters, C)):
   samplers/HMC.py:86-134, 138-219, 259-314

@@ -1,8 +1,9 @@
 """Pins the CPU oracle (oracle/mcmc_oracle.c).
 
 The reference ships no golden vectors and jax is not installable
-here, so the oracle is "parity unpinned" against the reference itself; what CAN
-be pinned is checked here:
+here; the oracle is pinned against the reference's own source in
+tests/test_reference_golden_cpu.py (reference files run on a torch-fp64 stand-in
+for jax).  This file holds the other pins:
   * Philox4x32-10 against the published Random123 known-answer vectors,
   * the known-answer facts derived from the reference source,
   * every gradient against torch fp64 autograd of the log-density as coded,
