@@ -27,6 +27,15 @@
 namespace mcmc {
 
 constexpr int kStepUnroll = MCMC_STEP_UNROLL;
+// Long trajectories run an instantiation register-allocated for SIX resident blocks per SM (168 registers, 3 warps per
+// scheduler; ptxas spills ~330 B per thread, none of it inside the trajectory loop): the loop then keeps the fp64 pipe
+// 97% busy instead of 88%, while the per-iteration part gets ~30% slower (instruction-fetch stalls, spill reloads) —
+// a net gain from L ~ 90 upwards (profiles/hmc_occupancy_sweep_r01.txt: L=128 +4.8%, L=64 -2%, L=16 -11%).
+#ifndef MCMC_HMC_DENSE_MIN_L
+#define MCMC_HMC_DENSE_MIN_L 96
+#endif
+constexpr int kHmcDenseMinL = MCMC_HMC_DENSE_MIN_L;
+constexpr int kHmcDenseBlocks = 6;
 
 struct HmcKArgs {
   McmcParams p;
@@ -78,8 +87,8 @@ struct HmcSmem {
 
 // WELF: the per-chain Welford accumulation (tuning batches) is compiled only into its own instantiation, so that the
 // sampling kernel's register allocation does not depend on it
-template <int TID, int DS, bool FRICTION, int BLOCK, bool WELF = false>
-__global__ void __launch_bounds__(BLOCK, 1) hmc_kernel(const HmcKArgs a) {
+template <int TID, int DS, bool FRICTION, int BLOCK, bool WELF = false, int MINB = 1>
+__global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
   constexpr int N = DS > 0 ? DS : MCMC_DYN_MAXD;
   const int n = DS > 0 ? DS : a.p.n_dim;
   const int L = a.p.num_steps;
@@ -449,7 +458,7 @@ __global__ void __launch_bounds__(BLOCK, 1) hmc_kernel(const HmcKArgs a) {
 }
 
 // host-side launcher for one (target, D-variant)
-template <int TID, int DS, bool FRICTION, int BLOCK, bool WELF>
+template <int TID, int DS, bool FRICTION, int BLOCK, bool WELF, int MINB = 1>
 int launch_hmc_variant_w(const Launch& l) {
   HmcKArgs a;
   a.p = l.p;
@@ -458,7 +467,7 @@ int launch_hmc_variant_w(const Launch& l) {
   const int n = l.p.n_dim;
   const HmcSmem<DS, BLOCK> lay(n, l.p.num_steps, target_table_len(TID, n), WELF);
   const size_t smem = lay.total_doubles() * sizeof(double);
-  auto kern = hmc_kernel<TID, DS, FRICTION, BLOCK, WELF>;
+  auto kern = hmc_kernel<TID, DS, FRICTION, BLOCK, WELF, MINB>;
   if (smem > 227 * 1024) {
     set_error("hmc: %zu bytes of shared memory needed (D=%d, L=%d) exceed 227 KB", smem, n, l.p.num_steps);
     return MCMC_ENOTSUP;
@@ -520,6 +529,8 @@ int launch_hmc_variant_w(const Launch& l) {
 template <int TID, int DS, bool FRICTION, int BLOCK>
 int launch_hmc_variant(const Launch& l) {
   const bool welf = (l.p.flags & MCMC_FLAG_ACCUM_WELFORD) && l.b.welford_mean && l.b.welford_m2;
+  if (DS == 20 && !FRICTION && !welf && l.p.num_steps >= kHmcDenseMinL && !getenv("MCMC_HMC_NO_DENSE"))
+    return launch_hmc_variant_w<TID, DS, FRICTION, BLOCK, false, (DS == 20 && !FRICTION) ? kHmcDenseBlocks : 1>(l);
   return welf ? launch_hmc_variant_w<TID, DS, FRICTION, BLOCK, true>(l) : launch_hmc_variant_w<TID, DS, FRICTION, BLOCK, false>(l);
 }
 

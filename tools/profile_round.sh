@@ -22,7 +22,7 @@ for L in 16 128; do
 done
 step $NCU_FULL -k regex:nuts_kernel -s 1 -c 1 -f -o $O/nuts_rb_$TAG \
     python tools/perf_hmc.py --sampler nuts --samples 96 --Ls 1 --eps 0.02 > $O/ncu_nuts_$TAG.log 2>&1 || echo "nuts capture failed" >&2
-step $NCU_FULL -k regex:rwmh_kernel -s 1 -c 1 -f -o $O/rwmh_$TAG \
+step $NCU_FULL -k regex:rwmh -s 1 -c 1 -f -o $O/rwmh_$TAG \
     python tools/perf_hmc.py --sampler rwmh --target standard_normal --chains 1048576 --samples 64 --Ls 1 --eps 0.5 \
     > $O/ncu_rwmh_$TAG.log 2>&1 || echo "rwmh capture failed" >&2
 ls -la $O | tail -20
