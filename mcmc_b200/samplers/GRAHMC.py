@@ -15,6 +15,7 @@ import torch
 
 from .. import _abi
 from ..benchmarks.targets import resolve_log_prob
+from ..random import split
 from ..runtime import run_sampler
 from .HMC import _pack, hmc_init
 
@@ -91,3 +92,22 @@ def rahmc_run(key, log_prob_fn, init_position, step_size: float, num_steps: int,
                       burn_in=int(burn_in), inv_mass_matrix=inv_mass_matrix, track_proposals=bool(track_proposals),
                       inject=_inject, variant=_variant, chain_offset=_chain_offset)
     return _pack(out, RAHMCState, track_proposals)
+
+
+def rahmc_step(state: RAHMCState, step_size: float, num_steps: int, gamma_max: float, steepness: float, key, log_prob_fn,
+               inv_mass_matrix=None, friction_schedule=None, return_proposal: bool = False, *,
+               _inject: Optional[dict] = None, _variant: Optional[str] = None, _chain_offset: int = 0):
+    """One GRAHMC transition from `state` (samplers/GRAHMC.py:265-349; note the reference's argument order, which
+    differs from hmc_step's): (next_key, new_state)[, proposal_pos, proposal_log_prob, delta_H]."""
+    tag = resolve_log_prob(log_prob_fn)
+    key, step_key = split(key)
+    out = run_sampler(_abi.SAMPLER_GRAHMC, tag, state.position, key=step_key, step_size=float(step_size),
+                      num_steps=int(num_steps), gamma=float(gamma_max),
+                      steepness=float(steepness if steepness is not None else 1.0),
+                      schedule_id=_schedule_id(friction_schedule), num_samples=1, burn_in=0,
+                      inv_mass_matrix=inv_mass_matrix, track_proposals=bool(return_proposal), inject=_inject,
+                      variant=_variant, chain_offset=_chain_offset)
+    new_state = RAHMCState(out["final_q"], out["final_lp"], out["final_g"], state.accept_count + out["accept_count"])
+    if return_proposal:
+        return key, new_state, out["prop_q"][0], out["prop_lp"][0], out["delta_h"][0]
+    return key, new_state

@@ -12,6 +12,7 @@ import torch
 
 from .. import _abi
 from ..benchmarks.targets import resolve_log_prob
+from ..random import split
 from ..runtime import ensure_batched, run_sampler, target_eval, to_device, _device
 
 
@@ -50,3 +51,21 @@ def hmc_run(key, log_prob_fn, init_position, step_size: float, num_steps: int, n
                       inv_mass_matrix=inv_mass_matrix, track_proposals=bool(track_proposals), inject=_inject,
                       variant=_variant, chain_offset=_chain_offset)
     return _pack(out, HMCState, track_proposals)
+
+
+def hmc_step(state: HMCState, log_prob_fn, step_size: float, num_steps: int, key, inv_mass_matrix=None,
+             return_proposal: bool = False, *, _inject: Optional[dict] = None, _variant: Optional[str] = None,
+             _chain_offset: int = 0):
+    """One HMC transition from `state` (samplers/HMC.py:138-219): (next_key, new_state) and, with return_proposal,
+    + (proposal_pos, proposal_log_prob, delta_H).  As in the reference the key is split once (`key, step_key`) and the
+    step draws from step_key; the launch is a one-iteration hmc_run, which re-derives the cached log-prob and gradient
+    from state.position (the same values bit for bit for a state this package produced)."""
+    tag = resolve_log_prob(log_prob_fn)
+    key, step_key = split(key)
+    out = run_sampler(_abi.SAMPLER_HMC, tag, state.position, key=step_key, step_size=float(step_size),
+                      num_steps=int(num_steps), num_samples=1, burn_in=0, inv_mass_matrix=inv_mass_matrix,
+                      track_proposals=bool(return_proposal), inject=_inject, variant=_variant, chain_offset=_chain_offset)
+    new_state = type(state)(out["final_q"], out["final_lp"], out["final_g"], state.accept_count + out["accept_count"])
+    if return_proposal:
+        return key, new_state, out["prop_q"][0], out["prop_lp"][0], out["delta_h"][0]
+    return key, new_state

@@ -7,6 +7,7 @@ import torch
 
 from .. import _abi
 from ..benchmarks.targets import resolve_log_prob
+from ..random import split
 from ..runtime import ensure_batched, run_sampler, target_eval, to_device, _device
 
 
@@ -34,3 +35,13 @@ def rwMH_run(key, log_prob_fn, init_position, num_samples: int, scale: float, bu
                       chain_offset=_chain_offset)
     state = RWMState(out["final_q"], out["final_lp"], out["accept_count"])
     return out["samples"], out["log_probs"], out["accept_rate"], state
+
+
+def rwMH_step(state: RWMState, log_prob_fn, scale: float, key, *, _inject: Optional[dict] = None,
+              _variant: Optional[str] = None, _chain_offset: int = 0):
+    """One random-walk Metropolis transition from `state` (samplers/RWMH.py:73-119): (next_key, new_state)."""
+    tag = resolve_log_prob(log_prob_fn)
+    key, step_key = split(key)
+    out = run_sampler(_abi.SAMPLER_RWMH, tag, state.position, key=step_key, step_size=float(scale), num_samples=1,
+                      burn_in=0, inject=_inject, variant=_variant, chain_offset=_chain_offset)
+    return key, RWMState(out["final_q"], out["final_lp"], state.accept_count + out["accept_count"])

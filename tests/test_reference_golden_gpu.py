@@ -45,3 +45,50 @@ def test_quickstart_signature_matches_reference_source(gpu_lib):
                       inject=dict(z=torch.from_numpy(c["z"]).cuda(), u=torch.from_numpy(c["u"]).cuda()))
     assert relerr(out["samples"].cpu().numpy(), c["samples"]) <= TOL
     assert relerr(out["log_probs"].cpu().numpy(), c["log_probs"]) <= TOL
+
+
+@pytest.mark.parametrize("cid", ["hmc/rosenbrock", "hmc/rosenbrock/L32_unit_mass", "grahmc/tanh/neals_funnel",
+                                 "grahmc/none/standard_normal_D10", "rwmh/student_t", "nuts/rosenbrock"])
+def test_step_api_replays_reference_run(gpu_lib, cid):
+    """The secondary API (hmc_step / rahmc_step / rwMH_step / nuts_step, reference argument orders): B+S single
+    transitions from *_init, each fed the reference run's draws of that iteration, retrace the reference's *_run —
+    which is a lax.scan of the same step function (HMC.py:268-311)."""
+    import torch
+    from mcmc_b200 import samplers as SM
+    from mcmc_b200.benchmarks import targets as T
+    from reference_cases import _TARGET_KW
+    c = CASES[cid]
+    m = c["meta"]
+    f = getattr(T, m["target"])(dim=m["D"], **_TARGET_KW[m["target"]]).log_prob_fn
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    w = cu(c["inv_mass"])
+    eps, B, S = float(c["eps"]), m["B"], m["S"]
+    init = {"hmc": SM.hmc_init, "grahmc": SM.rahmc_init, "rwmh": SM.rwMH_init, "nuts": SM.nuts_init}[m["sampler"]]
+    state = init(cu(c["q0"]), f)
+    key = 7
+    pos, lps, depths = [], [], []
+    for it in range(B + S):
+        inj = dict(z=cu(c["z"][it:it + 1]), u=cu(c["u"][it:it + 1]))
+        if m["sampler"] == "hmc":
+            key, state, prop_q, prop_lp, dh = SM.hmc_step(state, f, eps, m["L"], key, w, return_proposal=True, _inject=inj)
+            if it >= B:
+                assert relerr(prop_q.cpu().numpy(), c["prop_q"][it - B]) <= TOL
+                assert relerr(dh.cpu().numpy(), c["delta_h"][it - B]) <= TOL
+        elif m["sampler"] == "grahmc":
+            sched = None if m["sched"] is None else SM.get_friction_schedule(m["sched"])
+            key, state = SM.rahmc_step(state, eps, m["L"], m["gamma"], m["steep"], key, f, w, friction_schedule=sched, _inject=inj)
+        elif m["sampler"] == "rwmh":
+            key, state = SM.rwMH_step(state, f, eps, key, _inject=inj)
+        else:
+            inj.update(dir_u=cu(c["dir_u"][it:it + 1]), prop_u=cu(c["prop_u"][it:it + 1]))
+            key, state, d, _ = SM.nuts_step(state, f, eps, key, w, max_tree_depth=m["md"], _inject=inj)
+            depths.append(d.cpu().numpy())
+        pos.append(state.position.cpu().numpy())
+        lps.append(state.log_prob.cpu().numpy())
+    assert relerr(np.stack(pos[B:]), c["samples"]) <= TOL
+    assert relerr(np.stack(lps[B:]), c["log_probs"]) <= TOL
+    assert relerr(state.position.cpu().numpy(), c["final_q"]) <= TOL
+    if m["sampler"] == "nuts":
+        assert np.array_equal(np.stack(depths[B:]), c["tree_depths"])
+    if B == 0:
+        assert np.array_equal(state.accept_count.cpu().numpy(), c["accept_count"])
