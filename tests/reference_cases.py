@@ -47,3 +47,31 @@ def run_case(backend, c, variant_kw=None):
     if m["sampler"] == "nuts":
         kw.update(dir_u=c["dir_u"], prop_u=c["prop_u"])
     return backend.run(sampler, p, c["q0"], **kw)
+
+
+QUICKSTART_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_quickstart_golden.npz")
+
+
+def run_quickstart(backend):
+    """BASELINE configs[0] (README.md:41-71) through `backend` with the reference run's recorded draws; returns
+    (outputs, fixture)."""
+    c = dict(np.load(QUICKSTART_PATH))
+    tag = T.resolve_log_prob(T.standard_normal(dim=10, with_norm_const=False).log_prob_fn)   # README's -0.5*sum(x**2)
+    p = backend.make_params(tag.target_id, tag.target_params, 4, 10, 1000, 500, 16, 0.05, gamma=1.0, steepness=0.5,
+                            schedule_id=_abi.SCHEDULE_IDS["tanh"], rng_mode=_abi.RNG_INJECTED)
+    return backend.run(_abi.SAMPLER_GRAHMC, p, c["q0"], z=c["z"], u=c["u"]), c
+
+
+def check_quickstart(got, c, tol):
+    from helpers import relerr
+    assert np.array_equal(got["accept_count"], c["accept_count"])
+    assert np.array_equal(got["accept_rate"], c["accept_rate"])
+    worst = 0.0
+    for a, b in ((got["log_probs"], c["log_probs"]), (got["samples"][::20], c["samples_every20"]),
+                 (got["samples"][-1], c["samples_last"]), (got["final_q"], c["final_q"]), (got["final_lp"], c["final_lp"]),
+                 (got["final_g"], c["final_g"]), (got["samples"].mean(axis=(0, 1)), c["sample_mean"]),
+                 (got["samples"].var(axis=(0, 1)), c["sample_var"])):
+        e = relerr(a, b)
+        worst = max(worst, e)
+        assert e <= tol, e
+    return worst

@@ -92,3 +92,11 @@ def test_step_api_replays_reference_run(gpu_lib, cid):
         assert np.array_equal(np.stack(depths[B:]), c["tree_depths"])
     if B == 0:
         assert np.array_equal(state.accept_count.cpu().numpy(), c["accept_count"])
+
+
+@pytest.mark.parametrize("variant", ["strict", "fast"])
+def test_cuda_matches_reference_quickstart_at_full_size(gpu_lib, variant):
+    """BASELINE configs[0] at full size against the reference's own source (4 chains x 1500 iterations x L=16)."""
+    from reference_cases import check_quickstart, run_quickstart
+    got, c = run_quickstart(GpuBackend(variant))
+    check_quickstart(got, c, 1e-10)
