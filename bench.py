@@ -42,10 +42,12 @@ INV_MASS = np.linspace(0.5, 2.0, D)  # a non-trivial diagonal M^-1 to exercise t
 SEED = (0, 0)
 # algorithmic fp64 flops of THIS kernel's formulation (FMA = 2), DESIGN.md "flop model"
 # dram__bytes_read.sum + dram__bytes_write.sum of one hmc_kernel launch at the bench shape (ncu --set full captures of
-# L=16 and L=128: 802.3 MB and 778.6 MB, profiles/ncu_hmc_L{16,128}_r01c.txt) — a constant from the profile, not a live
+# L=16 and L=128: 803.7 MB and 1011.9 MB, profiles/ncu_hmc_L{16,128}_r01e.txt; the L=128 launch is the 168-register
+# instantiation, whose register spills add ~245 MB of local-memory write-back) — a constant from the profile, not a live
 # measurement; the algorithmic bytes are the stored samples + log-probs, the initial state read and the final q / g written
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 790.4e6
-NCU_TRAFFIC_SOURCE = "profiles/ncu_hmc_L16_r01c.txt, profiles/ncu_hmc_L128_r01c.txt (mean of the two launches)"
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 907.8e6
+NCU_TRAFFIC_SOURCE = ("profiles/ncu_hmc_L16_r01e.txt (803.7 MB), profiles/ncu_hmc_L128_r01e.txt (1011.9 MB incl. spill write-back); "
+                      "mean of the two launches")
 F_STEP = 231.0           # per leapfrog step of one 20-D rosenbrock chain: 80 integrator (2 DFMA/dim) + 151 gradient (75 DFMA + 1 DMUL)
 F_ITER = 190.0           # per MH iteration outside the trajectory (momentum scaling, two kinetic energies, value)
 
@@ -336,7 +338,7 @@ def run_gpu_arm(args) -> None:
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                          "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH, "traffic_source": NCU_TRAFFIC_SOURCE,
                          "algorithmic_bytes_per_launch": wb_bytes + 3 * C * D * 8 + 2 * C * 8,
-                         "kernel": "mcmc::hmc_kernel<6, 20, false, 64> (rosenbrock, D=20, HMC)",
+                         "kernel": "mcmc::hmc_kernel<6, 20, false, 64, false, 1> at L=16/32/64 and <..., 6> (6 blocks/SM) at L=128 (rosenbrock, D=20, HMC)",
                          "peak_source": "mcmc_fp64_peak_probe measured in this run (register-resident DFMA, all SMs); "
                                         "MEASURED_PEAKS.json has no fp64 entry; nominal 37.2 TFLOP/s",
                          "flop_model": f"{F_STEP:.0f} flops per leapfrog step + {F_ITER:.0f} per MH iteration (FMA=2), "
