@@ -433,6 +433,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
     if (tid == 0) st_release_u32(a.flags + grp, (unsigned int)chunk + 1u);
   } else {
   // ---- epilogue: final state, acceptance statistics
+  if (S == 0) acc = 0;  // the counters are reset after burn-in even when nothing is sampled (HMC.py:276-282)
   load_row<DS>(q, my_q, n);
 #pragma unroll
   for (int d = 0; d < n; ++d) g[d] = sm_g[d * BLOCK + tid];

@@ -416,6 +416,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) hmc_ws_kernel(const HmcKArgs a)
       consumer_bar();
       if (tid == 0) st_release_u32(a.flags + grp, (unsigned int)chunk + 1u);
     } else {
+      if (S == 0) acc = 0;  // reset after burn-in even when nothing is sampled (HMC.py:276-282)
       load_row<DS>(q, my_q, n);
 #pragma unroll
       for (int d = 0; d < n; ++d) g[d] = wg[d * 32 + lane];

@@ -351,6 +351,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
         if (it == it_item_end) {
           // ---- item finished: the chain's state goes home (or, after the last iteration, to the outputs)
           if (it == B + S) {
+            if (S == 0) acc = 0;  // reset after burn-in even when nothing is sampled (NUTS.py:494-500)
             acc_total += (unsigned long long)acc;
             if (a.b.accept_count) a.b.accept_count[chain] = acc;
             if (a.b.accept_rate) a.b.accept_rate[chain] = (float)acc / (float)S;  // NUTS.py:512

@@ -100,6 +100,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kRwmhMinBlocks : 1) rwmh_kerne
   }
   if (store) tw.finish();
 
+  if (S == 0) acc = 0;  // reset after burn-in even when nothing is sampled (RWMH.py:160-166)
   if (active) {
     if (a.b.accept_count) a.b.accept_count[chain] = acc;
     if (a.b.accept_rate) a.b.accept_rate[chain] = (float)acc / (float)S;  // RWMH.py:177
@@ -223,6 +224,7 @@ __global__ void __launch_bounds__(BLOCK, MCMC_RWMH_WARP_MINBLOCKS) rwmh_warp_ker
   if (lane == 0) bulk_wait_all();
   __syncwarp();
 
+  if (S == 0) acc = 0;  // reset after burn-in even when nothing is sampled (RWMH.py:160-166)
   if (active) {
     if (a.b.accept_count) a.b.accept_count[chain] = acc;
     if (a.b.accept_rate) a.b.accept_rate[chain] = (float)acc / (float)S;  // RWMH.py:177

@@ -378,6 +378,7 @@ static void hmc_chain(const McmcParams* p, const McmcBuffers* b, int64_t c, int 
       if (do_w) { wcount += 1.0; welford_fold(wmean, wm2, wcount, q, D); }
     }
   }
+  if (S == 0) acc = 0; /* counters are reset after burn-in even when nothing is sampled (HMC.py:276-282) */
   if (b->accept_count) b->accept_count[c] = acc;
   if (b->accept_rate) b->accept_rate[c] = (float)acc / (float)S; /* HMC.py:313 */
   if (b->final_q) memcpy(b->final_q + (size_t)c * D, q, sizeof(double) * D);
@@ -455,6 +456,7 @@ static void rwmh_chain(const McmcParams* p, const McmcBuffers* b, int64_t c, uns
       if (b->log_probs) b->log_probs[o] = lp;
     }
   }
+  if (S == 0) acc = 0; /* counters are reset after burn-in even when nothing is sampled (HMC.py:276-282) */
   if (b->accept_count) b->accept_count[c] = acc;
   if (b->accept_rate) b->accept_rate[c] = (float)acc / (float)S;
   if (b->final_q) memcpy(b->final_q + (size_t)c * D, q, sizeof(double) * D);
@@ -580,6 +582,7 @@ static void nuts_chain(const McmcParams* p, const McmcBuffers* b, int64_t c, uns
       if (do_w) { wcount += 1.0; welford_fold(wmean, wm2, wcount, q, D); }
     }
   }
+  if (S == 0) acc = 0; /* counters are reset after burn-in even when nothing is sampled (HMC.py:276-282) */
   if (b->accept_count) b->accept_count[c] = acc;
   if (b->accept_rate) b->accept_rate[c] = (float)acc / (float)S;
   if (b->final_q) memcpy(b->final_q + (size_t)c * D, q, sizeof(double) * D);

@@ -207,6 +207,8 @@ def hmc_run(target, init_q, step_size, num_steps, num_samples, z, u, burn_in=0, 
         if it >= burn_in:
             out["samples"].append(q.copy()); out["log_probs"].append(lp.copy())
     res = {k: np.array(v) for k, v in out.items()}
+    if num_samples == 0:
+        acc[:] = 0   # reset after burn-in even when nothing is sampled (HMC.py:276-282)
     res.update(accept_count=acc, accept_rate=acc.astype(np.float32) / np.float32(num_samples),
                final_q=q, final_lp=lp, final_g=g)
     return res
@@ -230,6 +232,8 @@ def rwmh_run(target, init_q, scale, num_samples, z, u, burn_in=0):
         acc += accept.astype(np.int32)
         if it >= burn_in:
             samples.append(q.copy()); lps.append(lp.copy())
+    if num_samples == 0:
+        acc[:] = 0
     return dict(samples=np.array(samples), log_probs=np.array(lps), accept_count=acc,
                 accept_rate=acc.astype(np.float32) / np.float32(num_samples), final_q=q, final_lp=lp)
 

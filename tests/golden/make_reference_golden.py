@@ -76,6 +76,16 @@ for _n in ("standard_normal", "gaussian_mixture", "student_t"):
     CASES.append(dict(id=f"rwmh/{_n}", sampler="rwmh", target=_n, C=6, D=20, S=8, B=3, L=0, seed=31))
 for _n, _md in (("standard_normal", 6), ("rosenbrock", 5), ("neals_funnel", 5), ("correlated_gaussian", 5)):
     CASES.append(dict(id=f"nuts/{_n}", sampler="nuts", target=_n, C=3, D=20, S=4, B=1, L=0, md=_md, seed=41))
+# edge cases: trajectories that overflow (non-finite guard HMC.py:199, reject), NUTS divergence (delta_max, NUTS.py:283) and the
+# depth cap; "state_only": proposals may be inf/nan in implementation-defined ways, so only the chain state is compared
+CASES.append(dict(id="hmc/rosenbrock/overflow", sampler="hmc", target="rosenbrock", C=6, D=20, S=4, B=1, L=8, seed=51, eps=0.45,
+                  state_only=True))
+CASES.append(dict(id="grahmc/linear/rosenbrock/overflow", sampler="grahmc", target="rosenbrock", sched="linear", steep=2.0, gamma=2.0,
+                  C=6, D=20, S=4, B=1, L=8, seed=52, eps=0.45, state_only=True))
+CASES.append(dict(id="nuts/neals_funnel/divergent", sampler="nuts", target="neals_funnel", C=4, D=20, S=4, B=1, L=0, md=6, seed=53,
+                  eps=2.5, state_only=True))
+CASES.append(dict(id="nuts/standard_normal/depth_cap2", sampler="nuts", target="standard_normal", C=4, D=20, S=5, B=0, L=0, md=2, seed=54,
+                  eps=0.05))
 
 
 def np64(x):
@@ -85,7 +95,7 @@ def np64(x):
 def run_case(c):
     kw, eps, init = TARGETS[c["target"]]
     eps = c.get("eps", eps)
-    if c["sampler"] == "nuts":
+    if c["sampler"] == "nuts" and "eps" not in c:
         eps = {"standard_normal": 0.4, "rosenbrock": 0.01, "neals_funnel": 0.1, "correlated_gaussian": 0.1}[c["target"]]
     if c["sampler"] == "rwmh":
         eps = 2.38 / np.sqrt(c["D"])   # dual_averaging.py:53

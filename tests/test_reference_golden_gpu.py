@@ -23,6 +23,8 @@ def test_cuda_matches_reference_source(gpu_lib, cid, variant):
         if k in c:
             assert np.array_equal(got[k].reshape(c[k].shape), c[k]), (cid, k)
     for k in FLOAT_KEYS:
+        if c["meta"].get("state_only") and k in ("prop_q", "prop_lp"):
+            continue   # overflowed proposals: inf / nan in implementation-defined places; the guard's effect is what is pinned
         if k in c and k in got:
             e = relerr(got[k].reshape(c[k].shape), c[k])
             assert e <= TOL, (cid, variant, k, e)
