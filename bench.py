@@ -355,9 +355,9 @@ def run_gpu_arm(args) -> None:
         }
         if world == 1 and not args.no_cpu_baseline:
             cpu_pass(2048, 8)  # wake the OpenMP team
-            r = cpu_pass(16384, 16)
+            r = cpu_pass(C, S_STORED // 2)   # about 5 s of CPU work on 16 threads
             line["cpu_baseline"] = {"value": r["value"], "unit": "grad-evals/s", "cores": r["cores"], "kind": "port",
-                                    "sample": f"16384 of {C} chains x 16 of {S_STORED} stored iterations x L grid "
+                                    "sample": f"all {C} chains x {S_STORED // 2} of {S_STORED} stored iterations x L grid "
                                               f"{list(L_GRID)} ({r['seconds']:.1f} s)",
                                     "note": "reference JAX CPU path unavailable on this box (jax not installed); C "
                                             "restatement oracle/mcmc_oracle.c, OpenMP over chains"}
