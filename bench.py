@@ -141,6 +141,24 @@ def cpu_pass(chains: int, samples: int, threads_note: bool = True) -> dict:
     return {"seconds": dt, "grad_evals": n_grad, "value": n_grad / dt, "cores": O.num_threads()}
 
 
+def ensure_built() -> None:
+    """The harness (not the product path, which fails loudly) builds the libraries when a fresh checkout has none.
+    Local rank 0 builds; the other ranks wait for the digest stamps the build writes after linking."""
+    from mcmc_b200 import _abi
+    csrc = os.path.join(ROOT, "mcmc_b200", "csrc")
+    need = list(_abi.LIB_PATHS.values()) + [os.path.join(ROOT, "oracle", "liboracle.so")]
+    stamps = [os.path.join(csrc, "build", v, "digest.txt") for v in ("fast", "strict")]
+    if all(os.path.exists(p) for p in need):
+        return
+    if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+        import __graft_entry__ as g
+        g.build()
+    else:
+        t0 = time.time()
+        while not all(os.path.exists(p) for p in need + stamps) and time.time() - t0 < 1200:
+            time.sleep(2.0)
+
+
 def run_reference_arm(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -374,6 +392,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    ensure_built()
     if args.impl == "reference":
         run_reference_arm(args)
     else:
