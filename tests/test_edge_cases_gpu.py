@@ -69,3 +69,31 @@ def test_wrappers_promote_1d_init_and_reject_3d(gpu_lib):
         SM.get_friction_schedule("no_such_schedule")   # GRAHMC.py:122
     with pytest.raises(NotImplementedError):
         SM.hmc_run(0, lambda v: -0.5 * (v ** 2).sum(), x, 0.1, 4, 3)   # untagged callable: no CPU fallback
+
+
+@pytest.mark.parametrize("sampler,L", SAMPLERS)
+def test_resume_from_final_state_position_equals_one_run(gpu_lib, oracle, sampler, L):
+    """Sampler-level resume as the reference does it (adaptation.py:215, run_benchmarks.py:614): the next call starts
+    from final_state.position and re-derives log-prob / gradient.  With the same draws, 4 + 5 iterations in two calls
+    reproduce 9 iterations in one call bit for bit."""
+    name, D, C_ = "rosenbrock", 20, 70
+    params, eps, init = TARGET_CASES[name]
+    rng = np.random.default_rng(5)
+    q0 = init(rng, C_, D)
+    z, u = rng.standard_normal((9, C_, D)), rng.random((9, C_))
+    du, pu = rng.random((9, C_, 5)), rng.random((9, C_, 5))
+
+    def run(q, lo, hi):
+        kw = dict(z=z[lo:hi], u=u[lo:hi])
+        if sampler == _abi.SAMPLER_NUTS:
+            kw.update(dir_u=du[lo:hi], prop_u=pu[lo:hi])
+        p = oracle.make_params(tid(name), params, C_, D, hi - lo, 0, L, eps, gamma=1.0, steepness=0.5, schedule_id=1,
+                               rng_mode=_abi.RNG_INJECTED, max_tree_depth=5)
+        return GpuBackend("fast").run(sampler, p, q, **kw)
+
+    whole = run(q0, 0, 9)
+    first = run(q0, 0, 4)
+    second = run(first["final_q"], 4, 9)
+    assert np.array_equal(np.concatenate([first["samples"], second["samples"]]), whole["samples"])
+    assert np.array_equal(np.concatenate([first["log_probs"], second["log_probs"]]), whole["log_probs"])
+    assert np.array_equal(first["accept_count"] + second["accept_count"], whole["accept_count"])
