@@ -125,10 +125,31 @@ class ClockSampler(threading.Thread):
 # ----------------------------------------------------------------------------------------------
 # CPU arm: the oracle port of the reference (bench.py is one of the few places allowed to run it)
 
+_NATIVE = {}
+
+
+def native_oracle():
+    """oracle/mcmc_oracle.c compiled on THIS host with -O3 -march=native and FMA contraction (the checker build is -O2,
+    generic x86-64, -ffp-contract=off): the CPU arm is timed on the fast build."""
+    from oracle import oracle as O
+    if "so" not in _NATIVE:
+        import tempfile
+        path = os.path.join(tempfile.mkdtemp(prefix="mcmc_oracle_native_"), "liboracle_native.so")
+        try:
+            O.build_native(path)
+            O.use_library(path)
+            _NATIVE["so"] = path
+            _NATIVE["flags"] = "-O3 -march=native -ffp-contract=fast -fopenmp"
+        except Exception as e:   # no compiler on the box: time the checker build and say so
+            _NATIVE["so"] = None
+            _NATIVE["flags"] = f"-O2 -ffp-contract=off -fopenmp (native build failed: {type(e).__name__})"
+    return O
+
+
 def cpu_pass(chains: int, samples: int, threads_note: bool = True) -> dict:
     """One pass over the L grid on `chains` chains with the C oracle (all OpenMP threads)."""
     from mcmc_b200 import _abi
-    from oracle import oracle as O
+    O = native_oracle()
     q0 = init_positions(0)[:chains]
     t0 = time.perf_counter()
     n_grad = 0
@@ -138,7 +159,7 @@ def cpu_pass(chains: int, samples: int, threads_note: bool = True) -> dict:
         r = O.run(_abi.SAMPLER_HMC, p, q0, inv_mass=INV_MASS)
         n_grad += int(r["counters"][1])
     dt = time.perf_counter() - t0
-    return {"seconds": dt, "grad_evals": n_grad, "value": n_grad / dt, "cores": O.num_threads()}
+    return {"seconds": dt, "grad_evals": n_grad, "value": n_grad / dt, "cores": O.num_threads(), "flags": _NATIVE["flags"]}
 
 
 def ensure_built() -> None:
@@ -181,7 +202,7 @@ def run_reference_arm(args) -> None:
         "config": workload_config(args.gpus),
         "cpu_baseline": {"value": val, "unit": "grad-evals/s", "cores": cores, "kind": "port", "sample": sample,
                          "note": "reference JAX CPU path unavailable on this box (jax not installed, no network); "
-                                 "this is the C restatement oracle/mcmc_oracle.c, OpenMP over chains"},
+                                 "this is the C restatement oracle/mcmc_oracle.c, OpenMP over chains, gcc " + _NATIVE.get("flags", "")},
         "e2e": {"value": val, "unit": "grad-evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -378,7 +399,7 @@ def run_gpu_arm(args) -> None:
                                     "sample": f"all {C} chains x {S_STORED // 2} of {S_STORED} stored iterations x L grid "
                                               f"{list(L_GRID)} ({r['seconds']:.1f} s)",
                                     "note": "reference JAX CPU path unavailable on this box (jax not installed); C "
-                                            "restatement oracle/mcmc_oracle.c, OpenMP over chains"}
+                                            "restatement oracle/mcmc_oracle.c, OpenMP over chains, gcc " + r["flags"]}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

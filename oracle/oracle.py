@@ -28,6 +28,23 @@ def build(force: bool = False) -> str:
     return _SO
 
 
+def build_native(out_path: str) -> str:
+    """The same source compiled for speed on THIS host (-O3 -march=native, FMA contraction allowed): what bench.py's
+    cpu_baseline / --impl reference legs time, so that the CPU number is not handicapped by the checker's strict flags.
+    Must be built on the machine that runs it (-march=native), hence not part of build()."""
+    cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"
+    subprocess.check_call([cc, "-O3", "-march=native", "-fPIC", "-std=c11", "-ffp-contract=fast", "-fopenmp", "-D_GNU_SOURCE",
+                           "-shared", "-o", out_path, os.path.join(_HERE, "mcmc_oracle.c"), "-lm"])
+    return out_path
+
+
+def use_library(path: str) -> None:
+    """Point this driver at another build of the oracle (bench.py: the -march=native one)."""
+    global _LIB, _SO
+    _SO = path
+    _LIB = None
+
+
 def lib() -> C.CDLL:
     global _LIB
     if _LIB is None:
