@@ -184,7 +184,7 @@ def run_reference_arm(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    chains, samples = 4096, 32   # bounded sample: 4096 of the 65,536 chains, 32 of the 64 stored iterations
+    chains, samples = 16384, 32   # bounded sample: 16,384 of the 65,536 chains, 32 of the 64 stored iterations (~0.5 s per step)
     for _ in range(args.warmup):
         cpu_pass(chains, samples)
     tot_t, tot_g, cores = 0.0, 0, 1
@@ -394,9 +394,9 @@ def run_gpu_arm(args) -> None:
         }
         if world == 1 and not args.no_cpu_baseline:
             cpu_pass(2048, 8)  # wake the OpenMP team
-            r = cpu_pass(C, S_STORED // 2)   # about 5 s of CPU work on 16 threads
+            r = cpu_pass(C, S_STORED)   # one whole step of the workload: about 4-5 s on 16 threads
             line["cpu_baseline"] = {"value": r["value"], "unit": "grad-evals/s", "cores": r["cores"], "kind": "port",
-                                    "sample": f"all {C} chains x {S_STORED // 2} of {S_STORED} stored iterations x L grid "
+                                    "sample": f"one whole step: all {C} chains x {S_STORED} stored iterations x L grid "
                                               f"{list(L_GRID)} ({r['seconds']:.1f} s)",
                                     "note": "reference JAX CPU path unavailable on this box (jax not installed); C "
                                             "restatement oracle/mcmc_oracle.c, OpenMP over chains, gcc " + r["flags"]}
