@@ -32,6 +32,17 @@
  *    (a cudaStream_t passed as void*), allocate nothing and never sync the
  *    host.  mcmc_run_host is the same path with HOST pointers (it owns the
  *    H2D/D2H copies and a cached device arena).
+ *  - alignment: every pointer must be aligned to its element type; samples / init_q aligned to 16 bytes take
+ *    the TMA bulk-store / 16-byte vector paths, pointers that are only 8-byte aligned take plain stores
+ *    (same results).
+ *  - co-residency: with more chains than resident threads the HMC/GRAHMC and NUTS launchers cut the run into
+ *    (chain group, iteration chunk) items claimed from an atomic queue; an item spins (acquire on a device flag)
+ *    until the item before it on the same chains has published its state.  That earlier item is always held by a
+ *    resident block because the grid is sized from cudaOccupancyMaxActiveBlocksPerMultiprocessor, which assumes
+ *    the library has the GPU's SM resources to itself while a sampler kernel runs.  Under MPS, a debugger, or a
+ *    concurrent kernel on another stream that occupies shared memory / registers first, set the environment
+ *    variable MCMC_NO_SPIN=1: every chain (group) is then ONE item, nothing waits, results are bit-identical,
+ *    and the last wave's tail (about 10% at 65,536 chains) is the price.
  *  - all arrays are row-major with the reference's shapes: samples (S,C,D),
  *    log_probs (S,C), state (C,D) / (C,), everything fp64 except
  *    accept_count (int32), accept_rate (float32), tree_depths (int32).
@@ -148,6 +159,8 @@ typedef struct McmcBuffers {
 } McmcBuffers;
 
 int mcmc_abi_version(void);
+/* "mcmc_b200 sm_100a fast|strict [+ws]": which build of the sources this library is */
+const char* mcmc_build_info(void);
 const char* mcmc_last_error(void);
 /* number of CUDA devices usable by this library (0 -> every compute entry fails) */
 int mcmc_device_count(void);

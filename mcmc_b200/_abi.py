@@ -77,7 +77,7 @@ BUFFER_FIELDS = [f[0] for f in McmcBuffers._fields_ if f[1] is _P and f[0] != "w
 
 # every symbol include/mcmc_b200.h declares
 EXPORTS = [
-    "mcmc_abi_version", "mcmc_last_error", "mcmc_device_count", "mcmc_set_device", "mcmc_workspace_bytes",
+    "mcmc_abi_version", "mcmc_build_info", "mcmc_last_error", "mcmc_device_count", "mcmc_set_device", "mcmc_workspace_bytes",
     "mcmc_hmc_run", "mcmc_grahmc_run", "mcmc_rwmh_run", "mcmc_nuts_run",
     "mcmc_run_host", "mcmc_host_arena_release", "mcmc_target_eval", "mcmc_friction_table",
     "mcmc_welford_finalize", "mcmc_chain_moments", "mcmc_sum_f64", "mcmc_fp64_peak_probe",
@@ -119,6 +119,7 @@ def lib(variant: str | None = None) -> C.CDLL:
     L = C.CDLL(path)
     L.mcmc_abi_version.restype = C.c_int
     L.mcmc_last_error.restype = C.c_char_p
+    L.mcmc_build_info.restype = C.c_char_p
     L.mcmc_device_count.restype = C.c_int
     L.mcmc_set_device.argtypes = [C.c_int]
     L.mcmc_workspace_bytes.argtypes = [C.c_int, C.POINTER(McmcParams), C.POINTER(C.c_size_t)]

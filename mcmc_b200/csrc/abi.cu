@@ -69,6 +69,11 @@ size_t hmc_workspace_bytes(const McmcParams& p) {
   return 256 + flag_bytes + (2 * C * D + C) * sizeof(double) + C * sizeof(int) + 256;
 }
 
+bool no_spin() {
+  const char* e = getenv("MCMC_NO_SPIN");
+  return e && e[0] && e[0] != '0';
+}
+
 int device_sm_count() {
   static int sms[64] = {0};
   int dev = 0;
@@ -294,27 +299,39 @@ int launch_rng_fill(const McmcParams& p, int64_t it_begin, int64_t it_end, doubl
 
 // ------------------------------------------------------------------ host arena (mcmc_run_host)
 
+// One arena + stream per device, each behind its own mutex: host callers driving different GPUs do not serialise on
+// each other and a device switch does not free / reallocate.
+constexpr int kMaxDevices = 64;
 struct Arena {
   std::mutex mu;
-  int device = -1;
   char* base = nullptr;
   size_t cap = 0;
   cudaStream_t stream = nullptr;
 };
-static Arena g_arena;
+static Arena g_arena[kMaxDevices];
 
-static int arena_reserve(int device, size_t bytes) {
-  if (g_arena.device != device || g_arena.cap < bytes) {
-    if (g_arena.base) { cudaSetDevice(g_arena.device); cudaFree(g_arena.base); g_arena.base = nullptr; g_arena.cap = 0; }
-    if (int rc = cuda_fail(cudaSetDevice(device), "cudaSetDevice")) return rc;
-    if (g_arena.stream && g_arena.device != device) { cudaStreamDestroy(g_arena.stream); g_arena.stream = nullptr; }
-    const size_t want = bytes + (bytes >> 3) + (1u << 20);
-    if (int rc = cuda_fail(cudaMalloc(&g_arena.base, want), "cudaMalloc(host arena)")) return rc;
-    g_arena.cap = want;
-    g_arena.device = device;
+// makes `device` current for the calling thread and restores the previous device on scope exit (a host framework
+// or a worker thread may have another device current)
+struct DeviceGuard {
+  int prev = -1;
+  int rc = MCMC_OK;
+  explicit DeviceGuard(int device) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
+    rc = cuda_fail(cudaSetDevice(device), "cudaSetDevice");
   }
-  if (!g_arena.stream)
-    if (int rc = cuda_fail(cudaStreamCreateWithFlags(&g_arena.stream, cudaStreamNonBlocking), "cudaStreamCreate")) return rc;
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+// caller holds a.mu and has made the arena's device current
+static int arena_reserve(Arena& a, size_t bytes) {
+  if (a.cap < bytes) {
+    if (a.base) { cudaFree(a.base); a.base = nullptr; a.cap = 0; }
+    const size_t want = bytes + (bytes >> 3) + (1u << 20);
+    if (int rc = cuda_fail(cudaMalloc(&a.base, want), "cudaMalloc(host arena)")) return rc;
+    a.cap = want;
+  }
+  if (!a.stream)
+    if (int rc = cuda_fail(cudaStreamCreateWithFlags(&a.stream, cudaStreamNonBlocking), "cudaStreamCreate")) return rc;
   return MCMC_OK;
 }
 
@@ -325,6 +342,18 @@ using namespace mcmc;
 extern "C" {
 
 int mcmc_abi_version(void) { return MCMC_ABI_VERSION; }
+const char* mcmc_build_info(void) {
+  return "mcmc_b200 sm_100a"
+#if MCMC_IS_FAITHFUL
+         " strict"
+#else
+         " fast"
+#endif
+#ifdef MCMC_WITH_WS
+         " +ws"
+#endif
+      ;
+}
 const char* mcmc_last_error(void) { return g_err; }
 int mcmc_device_count(void) { return have_device(); }
 int mcmc_set_device(int device) {
@@ -439,16 +468,27 @@ int mcmc_fp64_peak_probe(int iters, double* flops_out, float* ms_out, void* stre
 }
 
 int mcmc_host_arena_release(void) {
-  std::lock_guard<std::mutex> lk(g_arena.mu);
-  if (g_arena.base) { cudaSetDevice(g_arena.device); cudaFree(g_arena.base); }
-  if (g_arena.stream) cudaStreamDestroy(g_arena.stream);
-  g_arena.base = nullptr; g_arena.cap = 0; g_arena.stream = nullptr; g_arena.device = -1;
+  for (int dev = 0; dev < kMaxDevices; ++dev) {
+    Arena& a = g_arena[dev];
+    std::lock_guard<std::mutex> lk(a.mu);
+    if (!a.base && !a.stream) continue;
+    DeviceGuard dg(dev);
+    if (a.base) cudaFree(a.base);
+    if (a.stream) cudaStreamDestroy(a.stream);
+    a.base = nullptr; a.cap = 0; a.stream = nullptr;
+  }
   return MCMC_OK;
 }
 
 int mcmc_run_host(int sampler, const McmcParams* p, const McmcBuffers* h, int device) {
   if (int rc = validate(p, h, sampler)) return rc;
-  std::lock_guard<std::mutex> lk(g_arena.mu);
+  if (device < 0 || device >= have_device() || device >= kMaxDevices) { set_error("device %d not available", device); return MCMC_ECUDA; }
+  // the device is made current for THIS call whatever the thread had before (and restored on return): the launchers
+  // read the current device's SM count / occupancy and enqueue on this device's arena stream
+  DeviceGuard dg(device);
+  if (dg.rc) return dg.rc;
+  Arena& arena = g_arena[device];
+  std::lock_guard<std::mutex> lk(arena.mu);
   const size_t C = (size_t)p->n_chains, D = (size_t)p->n_dim, S = (size_t)p->num_samples;
   const size_t T = (size_t)(p->burn_in + p->num_samples);
   const size_t md = (size_t)(p->max_tree_depth > 0 ? p->max_tree_depth : 1);
@@ -494,9 +534,9 @@ int mcmc_run_host(int sampler, const McmcParams* p, const McmcBuffers* h, int de
               : (sampler == MCMC_SAMPLER_HMC || sampler == MCMC_SAMPLER_GRAHMC) ? hmc_workspace_bytes(*p) : 0;
   size_t total = ws + 256;
   for (auto& it : items) total += (it.bytes + 255) / 256 * 256;
-  if (int rc = arena_reserve(device, total)) return rc;
-  char* cur = g_arena.base;
-  cudaStream_t s = g_arena.stream;
+  if (int rc = arena_reserve(arena, total)) return rc;
+  char* cur = arena.base;
+  cudaStream_t s = arena.stream;
   for (auto& it : items) {
     *it.slot = cur;
     if (it.hsrc && it.bytes)

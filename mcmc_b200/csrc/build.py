@@ -36,7 +36,7 @@ def _units():
 def _digest(flags) -> str:
     h = hashlib.sha256(" ".join(flags).encode())
     for f in sorted(os.listdir(HERE)):
-        if f.endswith((".cu", ".cuh")):
+        if f.endswith((".cu", ".cuh", ".inc")):
             h.update(open(os.path.join(HERE, f), "rb").read())
     h.update(open(os.path.join(HERE, "..", "..", "include", "mcmc_b200.h"), "rb").read())
     return h.hexdigest()[:16]

@@ -87,6 +87,13 @@ size_t nuts_workspace_bytes(const McmcParams& p);
 int launch_rng_fill(const McmcParams& p, int64_t it_begin, int64_t it_end, double* z, double* logu, cudaStream_t s);
 size_t hmc_workspace_bytes(const McmcParams& p);
 int device_sm_count();
+// MCMC_NO_SPIN=1: no in-kernel wait on another block's progress.  The chunked schedulers of hmc_kernel.cuh and
+// nuts_kernel.cuh let an item wait (acquire on a flag) for the item that precedes it on the same chains; that earlier
+// item is always held by a RESIDENT block because the grids are sized from the occupancy query — true on a GPU the
+// library has to itself, not guaranteed under MPS, a debugger or a concurrent kernel that takes SM resources first.
+// With the switch every chain group / chain is one item (n_chunks = 1): nothing ever waits; the price is the tail
+// of the last wave (~10% at 65,536 chains).  Results are bit-identical either way.
+bool no_spin();
 
 inline int cuda_fail(cudaError_t e, const char* what) {
   if (e == cudaSuccess) return 0;

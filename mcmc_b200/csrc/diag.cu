@@ -27,9 +27,25 @@ __global__ void __launch_bounds__(256) rank_normalize_kernel(const double* __res
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const double x = v[i];
+  // extent [lo, hi] of the run of values equal to x: binary searches on the sorted array, and only when a neighbour
+  // ties (O(log n) per element however long the run — a constant column is one run of n)
   int64_t lo = i, hi = i;
-  while (lo > 0 && v[lo - 1] == x) --lo;
-  while (hi + 1 < n && v[hi + 1] == x) ++hi;
+  if (i > 0 && v[i - 1] == x) {
+    int64_t a = 0, b = i - 1;             // first index in [0, i-1] with v[.] == x  (v[b] == x holds)
+    while (a < b) {
+      const int64_t m = a + ((b - a) >> 1);
+      if (v[m] == x) b = m; else a = m + 1;
+    }
+    lo = a;
+  }
+  if (i + 1 < n && v[i + 1] == x) {
+    int64_t a = i + 1, b = n - 1;         // last index in [i+1, n-1] with v[.] == x  (v[a] == x holds)
+    while (a < b) {
+      const int64_t m = a + ((b - a + 1) >> 1);
+      if (v[m] == x) a = m; else b = m - 1;
+    }
+    hi = a;
+  }
   const double r = 0.5 * (double)(lo + hi) + 1.0;            // average of the 1-based ranks lo+1 .. hi+1
   const double p = (r - 0.375) / ((double)n + 0.25);
   out[perm[i]] = normcdfinv(p);

@@ -1,7 +1,11 @@
 // hmc_inst.cu — instantiates the HMC/GRAHMC kernels of ONE target (-DMCMC_TID=k),
 // so the nine targets compile in parallel.
 #include "hmc_kernel.cuh"
+#ifdef MCMC_WITH_WS
+// the warp-specialised variant (measured 4-6% slower, profiles/ncu_hmc_ws_r01.txt) is an experiment: compiled only with
+// -DMCMC_WITH_WS (python -m mcmc_b200.csrc.build --suffix _ws -DMCMC_WITH_WS) and then taken with MCMC_HMC_WS=1
 #include "hmc_ws_kernel.cuh"
+#endif
 
 #ifndef MCMC_TID
 #error "compile with -DMCMC_TID=<target id>"
@@ -11,7 +15,7 @@ namespace mcmc {
 
 template <>
 int launch_hmc<MCMC_TID>(const Launch& l, bool friction) {
-  // large batches under the native stream: the warp-specialised kernel (producer warps draw the momenta)
+#ifdef MCMC_WITH_WS
   if (l.p.n_dim == 20 || l.p.n_dim == 10) {
     bool used = false;
     int rc;
@@ -19,6 +23,7 @@ int launch_hmc<MCMC_TID>(const Launch& l, bool friction) {
     else rc = friction ? launch_hmc_ws<MCMC_TID, 10, true>(l, &used) : launch_hmc_ws<MCMC_TID, 10, false>(l, &used);
     if (rc != MCMC_OK || used) return rc;
   }
+#endif
   switch (l.p.n_dim) {
     case 20:
       return friction ? launch_hmc_variant<MCMC_TID, 20, true, 64>(l) : launch_hmc_variant<MCMC_TID, 20, false, 64>(l);

@@ -490,7 +490,7 @@ int launch_hmc_variant_w(const Launch& l) {
   const int64_t slots = (int64_t)per_sm * device_sm_count();
   const int64_t iters = l.p.burn_in + l.p.num_samples;
   const size_t need = hmc_workspace_bytes(l.p);
-  const bool tuning_off = getenv("MCMC_HMC_NO_QUEUE") != nullptr;
+  const bool tuning_off = getenv("MCMC_HMC_NO_QUEUE") != nullptr || no_spin();
   const char* force = getenv("MCMC_HMC_FORCE_CHUNKS");  // test hook: chunk even when one wave would do
   if (!tuning_off && slots > 0 && (groups > slots || force) && iters >= 2 && l.b.workspace &&
       l.b.workspace_bytes >= need) {

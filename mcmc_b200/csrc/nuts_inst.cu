@@ -8,15 +8,6 @@
 
 namespace mcmc {
 
-template <>
-int launch_nuts<MCMC_TID>(const Launch& l) {
-  switch (l.p.n_dim) {
-    case 20: return launch_nuts_variant<MCMC_TID, 20, 32>(l);
-    case 10: return launch_nuts_variant<MCMC_TID, 10, 32>(l);
-    default: return launch_nuts_variant<MCMC_TID, 0, 32>(l);
-  }
-}
-
 // vmap(value_and_grad(log_prob_fn)) over n points: the *_init functions (HMC.py:73) and
 // direct calls of a target's log_prob_fn from host code.
 template <int TID, int DS>
@@ -62,6 +53,15 @@ int launch_target_eval<MCMC_TID>(const McmcParams& p, const double* cov_inv, con
   else MCMC_TE(0);
 #undef MCMC_TE
   return cuda_fail(cudaGetLastError(), "target_eval launch");
+}
+
+template <>
+int launch_nuts<MCMC_TID>(const Launch& l) {
+  switch (l.p.n_dim) {
+    case 20: return launch_nuts_variant<MCMC_TID, 20, 32>(l);
+    case 10: return launch_nuts_variant<MCMC_TID, 10, 32>(l);
+    default: return launch_nuts_variant<MCMC_TID, 0, 32>(l);
+  }
 }
 
 }  // namespace mcmc

@@ -412,6 +412,15 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
   }
 }
 
+// burn_in + num_samples == 0: nuts_run returns the nuts_init state (NUTS.py:73-86,479-514) — no item ever runs, so the
+// outputs are produced here (accept_rate = 0 / 0 in float32, as count / num_samples gives in jax)
+static __global__ void nuts_empty_run_kernel(int64_t C, int32_t* __restrict__ accept_count, float* __restrict__ accept_rate) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  if (accept_count) accept_count[c] = 0;
+  if (accept_rate) accept_rate[c] = __int_as_float(0x7fc00000);   // 0 / 0
+}
+
 template <int TID, int DS, int BLOCK>
 int launch_nuts_variant(const Launch& l) {
   NutsKArgs a;
@@ -454,6 +463,16 @@ int launch_nuts_variant(const Launch& l) {
   a.queue = reinterpret_cast<unsigned int*>(w + ws.queue_off);
   a.flags = a.queue + 64;
   const int64_t T = l.p.burn_in + l.p.num_samples;
+  if (T == 0) {
+    if (l.b.final_lp || l.b.final_g)
+      if (int rc = launch_target_eval<TID>(l.p, l.b.cov_inv, l.b.init_q, C, l.b.final_lp, l.b.final_g, l.stream)) return rc;
+    if (l.b.final_q)
+      if (int rc = cuda_fail(cudaMemcpyAsync(l.b.final_q, l.b.init_q, (size_t)C * n * sizeof(double),
+                                             cudaMemcpyDeviceToDevice, l.stream), "memcpy(nuts final_q)"))
+        return rc;
+    nuts_empty_run_kernel<<<(unsigned)((C + 255) / 256), 256, 0, l.stream>>>(C, l.b.accept_count, l.b.accept_rate);
+    return cuda_fail(cudaGetLastError(), "nuts_empty_run launch");
+  }
   const bool native = l.p.rng_mode == MCMC_RNG_PHILOX;
   const char* chunk_env = getenv("MCMC_NUTS_CHUNK");  // test hook / tuning knob: iterations per item
   // segments of at most ws.tseg iterations (one segment unless the draw buffer would exceed its cap)
@@ -467,7 +486,7 @@ int launch_nuts_variant(const Launch& l) {
     // has a lane of its own and one item per chain is all there is to do
     int64_t ci = it1 - it0;
     if (chunk_env && atoll(chunk_env) > 0) ci = atoll(chunk_env);
-    else if (C > grid * 32) ci = (it1 - it0 + 5) / 6;
+    else if (C > grid * 32 && !no_spin()) ci = (it1 - it0 + 5) / 6;
     if (ci < 1) ci = 1;
     int64_t nch = (it1 - it0 + ci - 1) / ci;
     if (nch * C >= ((int64_t)1 << 32) - (grid * 32 + 1)) {  // the queue counter is 32-bit: fall back to longer items

@@ -28,6 +28,23 @@ def test_rank_normalize_with_ties(gpu_lib):
     assert np.array_equal(vals.cpu().numpy(), np.sort(x.reshape(-1)))
 
 
+def test_rank_normalize_constant_and_stuck_columns(gpu_lib):
+    """A column that never moved is ONE tie run of n elements: the run boundaries come from binary searches, so 4 M equal
+    values cost the same as 4 M distinct ones (a linear scan per element would be O(n^2) and effectively hang)."""
+    from mcmc_b200 import diagnostics as DG
+    n = 1 << 22
+    z, _ = DG.rank_normalize(torch.full((n,), 3.25, dtype=torch.float64, device="cuda"))
+    torch.cuda.synchronize()
+    assert float(z.abs().max()) < 1e-6                      # every element gets the middle rank -> Phi^-1(~0.5) ~ 0
+    assert torch.equal(z, z[0].expand_as(z))
+    # half the column stuck at one value, the rest distinct: against the NumPy restatement
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal(4096)
+    x[::2] = 0.125
+    z, _ = DG.rank_normalize(torch.from_numpy(x).cuda())
+    np.testing.assert_allclose(z.cpu().numpy(), O.z_scale(x), rtol=0, atol=2e-13)
+
+
 @pytest.mark.parametrize("n,C", [(50, 7), (128, 100), (257, 33), (900, 40)])
 def test_split_chain_stats_vs_numpy(gpu_lib, n, C):
     """n=900 exceeds the shared-memory tile and takes the global-scratch variant of the kernel."""

@@ -37,6 +37,21 @@ def test_burn_in_only_run_stores_nothing_and_advances_the_state(gpu_lib, oracle,
 
 
 @pytest.mark.parametrize("sampler,L", SAMPLERS)
+def test_empty_run_returns_the_init_state(gpu_lib, oracle, sampler, L):
+    """burn_in = num_samples = 0: the reference returns the *_init state (value [+ gradient] at the initial position,
+    zero counters, accept_rate = 0 / 0) — HMC.py:259-314, NUTS.py:479-514, RWMH.py:148-178."""
+    r, o = _run_both(oracle, sampler, L, C_=37, S=0, B=0)
+    q0 = TARGET_CASES["neals_funnel"][2](np.random.default_rng(77), 37, 20)
+    assert np.array_equal(r["final_q"], q0)
+    assert relerr(r["final_lp"], o["final_lp"]) <= 1e-10
+    if sampler != _abi.SAMPLER_RWMH:
+        assert relerr(r["final_g"], o["final_g"]) <= 1e-10
+        assert np.any(r["final_g"] != 0.0)
+    assert np.all(r["accept_count"] == 0) and np.all(np.isnan(r["accept_rate"]))
+    assert r["samples"].shape == (0, 37, 20)
+
+
+@pytest.mark.parametrize("sampler,L", SAMPLERS)
 def test_single_chain(gpu_lib, oracle, sampler, L):
     r, o = _run_both(oracle, sampler, L, C_=1, S=5, B=2)
     for k in ("samples", "log_probs", "final_q", "final_lp"):
