@@ -188,6 +188,14 @@ int mcmc_host_arena_release(void);
 int mcmc_target_eval(const McmcParams* p, const double* cov_inv, const double* q,
                      int64_t n, double* lp, double* grad, void* stream);
 
+/* The native random stream as a callable (the draws the samplers make in-kernel; counter layout in
+   mcmc_b200/csrc/philox.cuh and oracle/rng_common.h).  Replaces the reference's random.normal(k_momentum, (C, D)) /
+   random.uniform(k_accept, (C,)) call sites (HMC.py:172,205  GRAHMC.py:306,336  RWMH.py:98,106  NUTS.py:219,224):
+   for it in [it_begin, it_begin + n_it) and the p->n_chains chains of this shard (p->chain_offset, p->seed, p->n_dim)
+   z[((it - it_begin)*C + c)*D + d] = the N(0,1) momentum / proposal draws, log_u[(it - it_begin)*C + c] = log of the
+   accept / slice uniform (-inf for u = 0).  Device pointers, either may be NULL. */
+int mcmc_philox_fill(const McmcParams* p, int64_t it_begin, int64_t n_it, double* z, double* log_u, void* stream);
+
 /* s_i = exp(-gamma_i * eps/2), i = 0..L-1, written to a DEVICE array of L doubles
    (and gamma_i to gamma_out if not NULL) */
 int mcmc_friction_table(int schedule_id, int num_steps, double step_size, double gamma,

@@ -274,8 +274,8 @@ __global__ void __launch_bounds__(128) nuts_rng_fill_kernel(McmcParams p, int64_
   rng.logtab = sm_logtab;
   const uint32_t it = (uint32_t)(it_begin + t);
   double* row = z + (size_t)idx * n;
-  const bool vec = ((n & 1) == 0);
-  for (int j = 0; 2 * j < n; ++j) {
+  const bool vec = ((n & 1) == 0) && ((reinterpret_cast<uintptr_t>(z) & 15) == 0);
+  for (int j = 0; z && 2 * j < n; ++j) {
     double z0, z1;
     philox_normals_block(rng, it, (uint32_t)j, z0, z1);
     if (vec) {
@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(128) nuts_rng_fill_kernel(McmcParams p, int64_
       if (2 * j + 1 < n) row[2 * j + 1] = z1;
     }
   }
-  logu[idx] = philox_accept_log_uniform(rng, it);
+  if (logu) logu[idx] = philox_accept_log_uniform(rng, it);
 }
 
 int launch_rng_fill(const McmcParams& p, int64_t it_begin, int64_t it_end, double* z, double* logu, cudaStream_t s) {
@@ -389,6 +389,14 @@ int mcmc_target_eval(const McmcParams* p, const double* cov_inv, const double* q
   if (p->target_id == MCMC_TARGET_DENSE_GAUSSIAN && (!cov_inv || p->n_dim > 64)) { set_error("dense_gaussian needs cov_inv, n_dim <= 64"); return MCMC_EINVAL; }
   if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
   return kEval[p->target_id](*p, cov_inv, q, n, lp, grad, (cudaStream_t)stream);
+}
+
+int mcmc_philox_fill(const McmcParams* p, int64_t it_begin, int64_t n_it, double* z, double* log_u, void* stream) {
+  if (!p) { set_error("null params"); return MCMC_EINVAL; }
+  if (p->n_dim < 1 || p->n_dim > MCMC_MAX_DIM || p->n_chains < 0 || n_it < 0 || it_begin < 0 ||
+      it_begin + n_it > 0xffffffffLL) { set_error("philox_fill: bad sizes"); return MCMC_EINVAL; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  return launch_rng_fill(*p, it_begin, it_begin + n_it, z, log_u, (cudaStream_t)stream);
 }
 
 int mcmc_friction_table(int schedule_id, int num_steps, double step_size, double gamma, double steepness, double* s_out,

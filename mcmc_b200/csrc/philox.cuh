@@ -51,7 +51,7 @@ __device__ __forceinline__ void normal_pair(const U4& o, const double* __restric
   const double lg = fast_log_u53(u53(o.x, o.y) + 1ull, logtab);   // log of a uniform in (0,1]
   const double rad = fast_sqrt_pos(-2.0 * lg);
   double s, c;
-  fast_sincos_u53(u53(o.z, o.w), &s, &c);                          // angle 2*pi*u2, u2 in [0,1)
+  fast_sincos_tab_u53(u53(o.z, o.w), logtab + MCMC_SCTAB_OFFSET, &s, &c);   // angle 2*pi*u2, u2 in [0,1)
   z0 = rad * c;
   z1 = rad * s;
 }
@@ -59,14 +59,14 @@ __device__ __forceinline__ void normal_pair(const U4& o, const double* __restric
 struct RngCtx {
   uint32_t k0, k1;       // key
   uint32_t gid_lo, gid_hi;
-  const double* logtab;  // shared-memory copy of kLogTabRaw
+  const double* logtab;  // shared-memory copy of kLogTabRaw (log table, then the sin/cos sector table)
 };
 
-// cooperative copy of the log table into shared memory (256 doubles); call before __syncthreads()
+constexpr int kRngTableDoubles = 768;
+// cooperative copy of the tables into shared memory (6 KB); call before __syncthreads()
 __device__ __forceinline__ void rng_table_fill(double* sm_logtab) {
-  for (int i = threadIdx.x; i < 256; i += blockDim.x) sm_logtab[i] = kLogTabRaw[i];
+  for (int i = threadIdx.x; i < kRngTableDoubles; i += blockDim.x) sm_logtab[i] = kLogTabRaw[i];
 }
-constexpr int kRngTableDoubles = 256;
 
 __device__ __forceinline__ void philox_normals_block(const RngCtx& r, uint32_t it, uint32_t block,
                                                      double& z0, double& z1) {

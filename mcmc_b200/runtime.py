@@ -177,6 +177,20 @@ def target_eval(tag, x, want_grad=True, device=None, variant=None):
     return lp, g
 
 
+def philox_fill(key, n_chains: int, n_dim: int, it_begin: int, n_it: int, chain_offset: int = 0, device=None,
+                variant=None):
+    """The native random stream of iterations [it_begin, it_begin + n_it): (z (n_it, C, D), log_u (n_it, C)) CUDA
+    tensors — exactly the normals and accept / slice log-uniforms the sampler kernels draw for these counters."""
+    dev = _device(device)
+    L = _abi.lib(variant)
+    p = make_params(0, [], n_chains, n_dim, 0, seed=as_key(key), chain_offset=chain_offset)
+    z = torch.empty((n_it, n_chains, n_dim), dtype=torch.float64, device=dev)
+    lu = torch.empty((n_it, n_chains), dtype=torch.float64, device=dev)
+    _abi.check(L.mcmc_set_device(dev.index), variant)
+    _abi.check(L.mcmc_philox_fill(C.byref(p), int(it_begin), int(n_it), _ptr(z), _ptr(lu), _stream_ptr(dev)), variant)
+    return z, lu
+
+
 def friction_table(schedule_id: int, num_steps: int, step_size: float, gamma: float, steepness: float,
                    device=None, variant=None):
     dev = _device(device)

@@ -26,7 +26,7 @@ int main() {
     const double x = -2 * b, sq = fast_sqrt_pos(x), sr = sqrt(x);
     if (sr > 0) rel_sq = fmax(rel_sq, fabs(sq - sr) / sr); else if (sq != 0) rel_sq = 1;
     double s, c;
-    fast_sincos_u53(k, &s, &c);
+    fast_sincos_tab_u53(k, kLogTabRaw + MCMC_SCTAB_OFFSET, &s, &c);
     const long double th = 2.0L * 3.14159265358979323846264338327950288L * (long double)k / 9007199254740992.0L;
     abs_sc = fmax(abs_sc, fmax(fabs(s - (double)sinl(th)), fabs(c - (double)cosl(th))));
   }
@@ -45,7 +45,7 @@ def test_fastmath_matches_libm(tmp_path):
     assert rel_log <= 4.5e-16      # <= 2 ulp
     assert abs_near1 <= 3e-17      # log(u) for u within 1e-12 of 1
     assert rel_sq <= 2.3e-16       # <= 1 ulp
-    assert abs_sc <= 3.4e-16
+    assert abs_sc <= 1.7e-16
 
 
 SRC_EXP = r'''
