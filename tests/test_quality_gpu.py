@@ -120,3 +120,76 @@ def test_warmup_large_c_fast_path(gpu_lib, sampler, sched):
     assert 0.05 < eps < 3.0
     if sampler == "grahmc":
         assert 0.01 <= info["gamma"] <= 5.0 and info["steepness"] == 0.5 and "friction_tuning" in info
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# The reference's own flow on the remaining BASELINE targets (run_benchmarks.py:468-712: run_adaptive_warmup -> *_run ->
+# gates), under the native Philox stream.  Settings probed with the CPU oracle (same flow, 512 chains): student_t and
+# log_gamma pass the full quality gate with 2000 draws after the 2500-step warmup; the bimodal mixture passes the hard
+# (usable) gate under NUTS.  The Bonferroni z-test has a 5% false-alarm rate by construction, so the assertion uses
+# |z| < 4 (0.1%) and reports the literal gate.
+
+@pytest.mark.parametrize("name,sampler,S,gate", [("student_t", "hmc", 2000, "quality"), ("log_gamma", "hmc", 2000, "quality"),
+                                                 ("gaussian_mixture", "nuts", 1000, "usable")])
+def test_gates_reference_flow_heavy_tailed_positive_and_bimodal_targets(gpu_lib, name, sampler, S, gate):
+    from mcmc_b200.benchmarks import targets as T
+    from mcmc_b200.samplers import hmc_run, nuts_run
+    from mcmc_b200.tuning import run_adaptive_warmup
+    tgt = T.get_target(name, D)
+    q0 = torch.as_tensor(np.asarray(tgt.init_sampler(3, C)), dtype=torch.float64).cuda()
+    eps, w, pos, info = run_adaptive_warmup(sampler, tgt.log_prob_fn, None, q0, key=7, num_warmup=2500, num_steps=16,
+                                            verbose=False)
+    assert info["num_da_updates"] == 26
+    if sampler == "hmc":
+        out = hmc_run(1, tgt.log_prob_fn, pos, eps, 16, S, inv_mass_matrix=w)
+    else:
+        out = nuts_run(1, tgt.log_prob_fn, pos, eps, S, inv_mass_matrix=w)
+    samples = out[0]
+    assert torch.isfinite(samples).all()
+    d, z, g, sw2, floor = _gates(samples, tgt, name, S)
+    assert g["usable"], (d["rhat_max"], d["ess_bulk_min"], d["ess_tail_min"])
+    assert z["max_z"] < 4.0, z["reason"]
+    if gate == "quality":
+        assert d["rhat_max"] < 1.01 and d["ess_tail_min"] >= 200, (d["rhat_max"], d["ess_tail_min"])
+    assert sw2 < 3 * floor + 0.05, (sw2, floor)
+    if name == "log_gamma":
+        assert float(samples.min()) > 0.0            # the support: a proposal outside has log p = -inf and is rejected
+
+
+@pytest.mark.parametrize("name,sampler,L", [("rosenbrock", "hmc", 16), ("rosenbrock", "hmc", 64), ("neals_funnel", "nuts", 0)])
+def test_gates_that_fail_fail_identically_on_the_oracle(gpu_lib, oracle, name, sampler, L):
+    """BASELINE configs 2 / 5 run the reference's way (warmup -> sample, 256 draws) do NOT pass the reference's hard gate:
+    on the 20-D rosenbrock(scale 0.1) split R-hat stays at 1.2-1.4 (the CPU oracle still reports 1.08 after 10,000 draws
+    per chain: the ridge mixes slowly under a diagonal metric), and on Neal's funnel the neck is unreachable at one step
+    size.  That is a property of the algorithm, not of the kernels: the CPU oracle run through the SAME host flow gives
+    the same statistics.  (Different chaotic realisations, same distribution: compared statistically.)"""
+    import helpers
+    from mcmc_b200 import _abi, diagnostics as DG
+    from mcmc_b200.benchmarks import targets as T
+    from mcmc_b200.samplers import hmc_run, nuts_run
+    from mcmc_b200.tuning import run_adaptive_warmup
+    from oracle import diagnostics_np as DN
+    Cq, S = 2048, 256
+    tgt = T.get_target(name, D)
+    tag = T.resolve_log_prob(tgt.log_prob_fn)
+    q0 = np.asarray(tgt.init_sampler(3, Cq))
+    kw = dict(key=7, num_warmup=2500, num_steps=max(L, 1), verbose=False)
+    eps, w, pos, _ = run_adaptive_warmup(sampler, tgt.log_prob_fn, None, torch.from_numpy(q0).cuda(), **kw)
+    if sampler == "hmc":
+        smp = hmc_run(1, tgt.log_prob_fn, pos, eps, L, S, inv_mass_matrix=w)[0]
+    else:
+        smp = nuts_run(1, tgt.log_prob_fn, pos, eps, S, inv_mass_matrix=w)[0]
+    dg = DG.compute_diagnostics(smp)
+    with pytest.MonkeyPatch.context() as m:
+        helpers.patch_tuning_to_oracle(m)
+        eps_o, w_o, pos_o, _ = run_adaptive_warmup(sampler, tgt.log_prob_fn, None, q0, **kw)
+    p = oracle.make_params(tag.target_id, tag.target_params, Cq, D, S, 0, L, eps_o, rng_mode=_abi.RNG_PHILOX, seed=(0, 1))
+    sid = _abi.SAMPLER_HMC if sampler == "hmc" else _abi.SAMPLER_NUTS
+    do = DN.compute_diagnostics(oracle.run(sid, p, pos_o.numpy(), inv_mass=w_o.numpy())["samples"])
+    assert eps == pytest.approx(eps_o, rel=0.1)
+    np.testing.assert_allclose(w.cpu().numpy(), w_o.numpy(), rtol=0.35)
+    assert dg["rhat_max"] >= 1.05 and do["rhat_max"] >= 1.05, (dg["rhat_max"], do["rhat_max"])     # usable gate: both fail
+    # the funnel's R-hat is set by a handful of chains deep in the neck and moves by +-30% between realisations
+    rtol = 0.15 if name == "rosenbrock" else 0.45
+    assert abs(dg["rhat_max"] - do["rhat_max"]) < rtol * do["rhat_max"], (dg["rhat_max"], do["rhat_max"])
+    assert 0.5 < dg["ess_bulk_min"] / do["ess_bulk_min"] < 2.0, (dg["ess_bulk_min"], do["ess_bulk_min"])
