@@ -143,6 +143,8 @@ def native_oracle():
         except Exception as e:   # no compiler on the box: time the checker build and say so
             _NATIVE["so"] = None
             _NATIVE["flags"] = f"-O2 -ffp-contract=off -fopenmp (native build failed: {type(e).__name__})"
+        # torchrun exports OMP_NUM_THREADS=1 to every worker: the CPU arm sizes its OpenMP team to the host's cores itself
+        _NATIVE["cores"] = O.use_all_cores()
     return O
 
 
@@ -248,7 +250,12 @@ def run_gpu_arm(args) -> None:
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+        # NCCL's INFO log (communicator ranks, NVLS / ring setup) goes to stderr; stdout carries rank 0's ONE JSON line.
+        # A value the launcher already exported is respected.
+        if "NCCL_DEBUG" not in os.environ:
+            os.environ["NCCL_DEBUG"] = "INFO"
+            os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT,ENV")
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     _abi.check(_abi.lib("fast").mcmc_set_device(local))
 
@@ -362,6 +369,63 @@ def run_gpu_arm(args) -> None:
     e2e_value = world * grad_per_step * e2e_steps / float(t.item())
     assert np.isfinite(host_out["log_probs"].numpy()).all()
 
+    # ---- second half of the metric: min-ESS/sec per L (run_benchmarks.py:179,188,712: ess_bulk_min / sample_time), from
+    # one more call per L at the bench shape; the bulk ESS is over ALL chains of the job (distributed diagnostics at N>1)
+    # and rhat_max is printed beside it: at eps = 0.02 and 64 draws these chains have NOT converged
+    from mcmc_b200 import diagnostics as DG
+    from mcmc_b200 import dist as mdist
+    ess = {}
+    for L in L_GRID:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        o = one_call(L, q0_dev, 2000)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        tt = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dg = DG.compute_diagnostics(o[0], distributed=world > 1)
+        ess[L] = {"ess_bulk_min": dg["ess_bulk_min"], "rhat_max": dg["rhat_max"], "kernel_ms": float(tt.item()),
+                  "min_ess_per_sec": dg["ess_bulk_min"] / (float(tt.item()) * 1e-3)}
+        del o
+
+    # ---- a communicating leg at every N, outside `value`: (1) one full run_adaptive_warmup of BASELINE configs[2]
+    # (GRAHMC tanh on the 20-D funnel, 32,768 chains per GPU, 2500 steps = 26 dual-averaging batches, device Welford;
+    # per batch the accept statistic and per window the chain variances cross the ranks), (2) R-hat / ESS of the last
+    # call's samples over all ranks' chains
+    from mcmc_b200.benchmarks.targets import neals_funnel
+    from mcmc_b200.tuning import run_adaptive_warmup
+    funnel = neals_funnel(D)
+    cw = 32768
+    qw = torch.as_tensor(np.asarray(funnel.init_sampler(77 + rank, cw)), dtype=torch.float64).to(dev)
+    comm = {}
+    for rep in range(2):                         # first pass warms every kernel variant and NCCL payload size
+        n0 = dict(mdist.COUNTERS)
+        barrier()
+        w0 = time.perf_counter()
+        eps_w, _, _, info_w = run_adaptive_warmup("grahmc", funnel.log_prob_fn, None, qw, key=5, num_warmup=2500,
+                                                  schedule_type="tanh", num_steps=16, verbose=False, tune_friction=False,
+                                                  chain_offset=rank * cw)
+        barrier()
+        tw = torch.tensor([time.perf_counter() - w0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+        comm = {"warmup_ms": 1e3 * float(tw.item()), "warmup_chains_per_gpu": cw,
+                "n_allreduce": mdist.COUNTERS["all_reduce"] - n0["all_reduce"], "da_updates": info_w["num_da_updates"],
+                "final_step_size": eps_w,
+                "warmup_grad_evals_per_sec": world * cw * 2500 * 16 / float(tw.item())}
+    for rep in range(2):
+        barrier()
+        w0 = time.perf_counter()
+        dgl = DG.compute_diagnostics(out[0], distributed=world > 1)
+        barrier()
+        td_ = torch.tensor([time.perf_counter() - w0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(td_, op=dist.ReduceOp.MAX)
+        comm["diagnostics_ms"] = 1e3 * float(td_.item())
+    comm["diagnostics_shape"] = [S_STORED, world * C, D]
+    comm["diagnostics_rhat_max"] = dgl["rhat_max"]
+
     if rank == 0:
         tot_kern_ms = sum(kern_ms.values())
         flops = sum(C * S_STORED * (L * F_STEP + F_ITER) for L in L_GRID) * args.steps
@@ -389,6 +453,9 @@ def run_gpu_arm(args) -> None:
                     "d2h_bytes_per_step": d2h * len(L_GRID), "steps": e2e_steps,
                     "what": "hmc_run(pinned host init) -> samples, log_probs, accept_rate, final state copied to pinned host"},
             "gpu_launches": len(L_GRID) * args.steps,
+            "min_ess_per_sec": {str(L): ess[L]["min_ess_per_sec"] for L in L_GRID},
+            "ess": {str(L): ess[L] for L in L_GRID},
+            "comm": comm,
             "clocks": clocks,
             "mean_accept_rate_last_call": acc_sum,
         }

@@ -22,6 +22,10 @@ import torch
 import torch.distributed as td
 
 
+# collectives issued through this module since import (bench.py reports the warmup's count)
+COUNTERS = {"all_reduce": 0, "all_gather": 0, "all_to_all": 0}
+
+
 def is_dist() -> bool:
     return td.is_available() and td.is_initialized()
 
@@ -46,12 +50,14 @@ def chain_shard(total_chains: int) -> Tuple[int, int]:
 def all_reduce_sum_(t: torch.Tensor) -> torch.Tensor:
     """In-place sum over ranks (identity without a process group)."""
     if is_dist() and world_size() > 1:
+        COUNTERS["all_reduce"] += 1
         td.all_reduce(t, op=td.ReduceOp.SUM)
     return t
 
 
 def all_reduce_max_(t: torch.Tensor) -> torch.Tensor:
     if is_dist() and world_size() > 1:
+        COUNTERS["all_reduce"] += 1
         td.all_reduce(t, op=td.ReduceOp.MAX)
     return t
 
@@ -63,6 +69,7 @@ def fused_sum(parts: Sequence[torch.Tensor]) -> list:
     if not (is_dist() and world_size() > 1):
         return [f.reshape(p.shape) for f, p in zip(flat, parts)]
     buf = torch.cat(flat)
+    COUNTERS["all_reduce"] += 1
     td.all_reduce(buf, op=td.ReduceOp.SUM)
     out, o = [], 0
     for p in parts:

@@ -644,6 +644,15 @@ void oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t
   philox4x32_10(ctr, key, out);
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to its workers; the timed CPU arm asks for the host's cores explicitly */
+void oracle_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 int oracle_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -69,6 +69,17 @@ def num_threads() -> int:
     return int(lib().oracle_num_threads())
 
 
+def use_all_cores() -> int:
+    """Size the OpenMP team to the cores this process may run on, whatever OMP_NUM_THREADS says (torchrun sets it to 1
+    in every worker's environment); returns the team size."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    lib().oracle_set_num_threads(int(n))
+    return num_threads()
+
+
 def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
