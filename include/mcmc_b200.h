@@ -57,7 +57,7 @@
 extern "C" {
 #endif
 
-#define MCMC_ABI_VERSION 1
+#define MCMC_ABI_VERSION 2
 
 /* error codes */
 #define MCMC_OK 0
@@ -156,6 +156,10 @@ typedef struct McmcBuffers {
   unsigned long long* counters; /* [4], zeroed by the callee at launch */
   void* workspace;          /* mcmc_workspace_bytes() bytes of device scratch */
   size_t workspace_bytes;
+  /* optional input (ABI 2): when not NULL the kernels read epsilon / the RWMH scale from this DEVICE double instead
+     of McmcParams.step_size — the dual-averaging state lives on the device (mcmc_da_update, element 5) and a whole
+     warmup is enqueued without a host round-trip */
+  const double* step_size_dev;
 } McmcBuffers;
 
 int mcmc_abi_version(void);
@@ -210,6 +214,21 @@ int mcmc_welford_finalize(const double* welford_m2, double count, int64_t n_chai
                           double* out_sum_var, void* workspace, size_t workspace_bytes, void* stream);
 int mcmc_chain_moments(const double* samples, int64_t num_samples, int64_t n_chains, int32_t n_dim,
                        double* welford_mean, double* welford_m2, double count_before, void* stream);
+/* Dual averaging on the device (tuning/dual_averaging.py:806-887: da_init / da_update / da_reset).  `state` is a DEVICE
+   array of MCMC_DA_STATE_DOUBLES doubles:
+     [0] log_step  [1] log_step_bar  [2] H_bar  [3] mu  [4] count m  [5] exp(log_step)  [6] exp(log_step_bar)
+     [7] the last accept statistic
+   mcmc_da_init: state of da_init(initial_step_size).  mcmc_da_update: accept_stat = accept_sum[0] / n_terms (accept_sum
+   a DEVICE double, e.g. the all-reduced in-kernel accept counter; with n_terms == 0 the divisor is accept_sum[1], so
+   that the sum and its term count can come out of the same all-reduce), then eta = 1/(m + t0), H_bar <- (1-eta) H_bar +
+   eta (target - stat), log_step = mu - sqrt(m)/omega H_bar, log_step_bar <- m^-kappa log_step + (1 - m^-kappa)
+   log_step_bar (first update: = log_step).  mcmc_da_reset: restart around the smoothed estimate (mu <- log_step_bar).
+   A sampler launched with McmcBuffers.step_size_dev = state + 5 steps with the current epsilon. */
+#define MCMC_DA_STATE_DOUBLES 8
+int mcmc_da_init(double* state, double initial_step_size, void* stream);
+int mcmc_da_update(double* state, const double* accept_sum, double n_terms, double target_accept, double omega, double t0,
+                   double kappa, void* stream);
+int mcmc_da_reset(double* state, void* stream);
 /* deterministic sum of n doubles -> out[0] (device pointers) */
 int mcmc_sum_f64(const double* x, int64_t n, double* out, void* workspace, size_t workspace_bytes,
                  void* stream);

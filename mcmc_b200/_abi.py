@@ -8,7 +8,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 SAMPLER_HMC, SAMPLER_GRAHMC, SAMPLER_RWMH, SAMPLER_NUTS = 0, 1, 2, 3
 
@@ -70,6 +70,7 @@ class McmcBuffers(C.Structure):
         ("tree_depths", _P), ("mean_accept_probs", _P),
         ("welford_mean", _P), ("welford_m2", _P), ("welford_count", C.c_double),
         ("counters", _P), ("workspace", _P), ("workspace_bytes", C.c_size_t),
+        ("step_size_dev", _P),
     ]
 
 
@@ -80,7 +81,7 @@ EXPORTS = [
     "mcmc_abi_version", "mcmc_build_info", "mcmc_last_error", "mcmc_device_count", "mcmc_set_device", "mcmc_workspace_bytes",
     "mcmc_hmc_run", "mcmc_grahmc_run", "mcmc_rwmh_run", "mcmc_nuts_run",
     "mcmc_run_host", "mcmc_host_arena_release", "mcmc_target_eval", "mcmc_philox_fill", "mcmc_friction_table",
-    "mcmc_welford_finalize", "mcmc_chain_moments", "mcmc_sum_f64", "mcmc_fp64_peak_probe",
+    "mcmc_welford_finalize", "mcmc_chain_moments", "mcmc_da_init", "mcmc_da_update", "mcmc_da_reset", "mcmc_sum_f64", "mcmc_fp64_peak_probe",
     "mcmc_rank_normalize", "mcmc_split_chain_stats_workspace", "mcmc_split_chain_stats",
 ]
 
@@ -131,6 +132,9 @@ def lib(variant: str | None = None) -> C.CDLL:
     L.mcmc_friction_table.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, _P, _P, _P]
     L.mcmc_welford_finalize.argtypes = [_P, C.c_double, C.c_int64, C.c_int32, _P, _P, C.c_size_t, _P]
     L.mcmc_chain_moments.argtypes = [_P, C.c_int64, C.c_int64, C.c_int32, _P, _P, C.c_double, _P]
+    L.mcmc_da_init.argtypes = [_P, C.c_double, _P]
+    L.mcmc_da_update.argtypes = [_P, _P, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, _P]
+    L.mcmc_da_reset.argtypes = [_P, _P]
     L.mcmc_sum_f64.argtypes = [_P, C.c_int64, _P, _P, C.c_size_t, _P]
     L.mcmc_fp64_peak_probe.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_float), _P]
     L.mcmc_rank_normalize.argtypes = [_P, _P, C.c_int64, _P, _P]

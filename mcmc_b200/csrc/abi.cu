@@ -229,6 +229,27 @@ __global__ void __launch_bounds__(256) chain_moments_kernel(const double* __rest
   m2[i] = mm;
 }
 
+// tuning/dual_averaging.py:818-887 on the device; one thread
+__global__ void da_init_kernel(double* st, double eps0) {
+  const double ls = log(eps0);
+  st[0] = ls; st[1] = ls; st[2] = 0.0; st[3] = ls; st[4] = 0.0; st[5] = eps0; st[6] = eps0; st[7] = 0.0;
+}
+__global__ void da_update_kernel(double* st, const double* __restrict__ accept_sum, double n_terms, double target,
+                                 double omega, double t0, double kappa) {
+  const double stat = accept_sum[0] / (n_terms > 0.0 ? n_terms : accept_sum[1]);
+  const double m = st[4] + 1.0;
+  const double eta = 1.0 / (m + t0);
+  const double hbar = (1.0 - eta) * st[2] + eta * (target - stat);
+  const double ls = st[3] - (sqrt(m) / omega) * hbar;
+  const double mk = pow(m, -kappa);
+  const double lsb = (m == 1.0) ? ls : mk * ls + (1.0 - mk) * st[1];
+  st[0] = ls; st[1] = lsb; st[2] = hbar; st[4] = m; st[5] = exp(ls); st[6] = exp(lsb); st[7] = stat;
+}
+__global__ void da_reset_kernel(double* st) {
+  const double cur = st[4] > 0.0 ? st[1] : st[0];
+  st[0] = cur; st[1] = cur; st[2] = 0.0; st[3] = cur; st[4] = 0.0; st[5] = exp(cur); st[6] = st[5];
+}
+
 __global__ void friction_table_kernel(int sched, int L, double eps, double gam, double steep, double* s_out,
                                       double* gamma_out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -410,6 +431,26 @@ int mcmc_friction_table(int schedule_id, int num_steps, double step_size, double
   return cuda_fail(cudaGetLastError(), "friction_table launch");
 }
 
+int mcmc_da_init(double* state, double initial_step_size, void* stream) {
+  if (!state || !(initial_step_size > 0.0)) { set_error("da_init: bad argument"); return MCMC_EINVAL; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  da_init_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state, initial_step_size);
+  return cuda_fail(cudaGetLastError(), "da_init launch");
+}
+int mcmc_da_update(double* state, const double* accept_sum, double n_terms, double target_accept, double omega, double t0,
+                   double kappa, void* stream) {
+  if (!state || !accept_sum || !(n_terms >= 0.0) || !(omega > 0.0)) { set_error("da_update: bad argument"); return MCMC_EINVAL; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  da_update_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state, accept_sum, n_terms, target_accept, omega, t0, kappa);
+  return cuda_fail(cudaGetLastError(), "da_update launch");
+}
+int mcmc_da_reset(double* state, void* stream) {
+  if (!state) { set_error("da_reset: null state"); return MCMC_EINVAL; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  da_reset_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state);
+  return cuda_fail(cudaGetLastError(), "da_reset launch");
+}
+
 #define MCMC_REDUCE_BLOCKS 256
 
 int mcmc_welford_finalize(const double* welford_m2, double count, int64_t n_chains, int32_t n_dim, double* out_sum_var,
@@ -512,6 +553,7 @@ int mcmc_run_host(int sampler, const McmcParams* p, const McmcBuffers* h, int de
   in(h->init_q, d.init_q, C * D);
   in(h->inv_mass, d.inv_mass, D);
   in(h->cov_inv, d.cov_inv, D * D);
+  in(h->step_size_dev, d.step_size_dev, 1);
   if (p->rng_mode == MCMC_RNG_INJECTED) {
     in(h->z_inject, d.z_inject, T * C * D);
     in(h->u_inject, d.u_inject, T * C);

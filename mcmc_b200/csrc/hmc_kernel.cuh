@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
   double* sm_wm = smem + lay.off_wm();
   double* sm_w2 = smem + lay.off_w2();
 
-  const double eps = a.p.step_size;
+  const double eps = a.b.step_size_dev ? __ldg(a.b.step_size_dev) : a.p.step_size;
   const double half_eps = 0.5 * eps;  // HMC.py:119 `half * step_sz`; GRAHMC.py:193
 
   // ---- prologue: per-dimension constants, friction table, target table

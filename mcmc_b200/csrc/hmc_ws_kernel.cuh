@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) hmc_ws_kernel(const HmcKArgs a)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + lay.off_bars());   // full[w][s] then empty[w][s]
   __shared__ unsigned int s_item;
 
-  const double eps = a.p.step_size;
+  const double eps = (a.b.step_size_dev ? __ldg(a.b.step_size_dev) : a.p.step_size);
   const double half_eps = 0.5 * eps;
 
   // ---- prologue (all 12 warps): constants, friction table, target table, barriers

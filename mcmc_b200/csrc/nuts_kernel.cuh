@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
   const bool do_w = (a.p.flags & MCMC_FLAG_ACCUM_WELFORD) && a.b.welford_mean && a.b.welford_m2;
   const bool injected = a.p.rng_mode == MCMC_RNG_INJECTED;
   const int max_depth = a.p.max_tree_depth;
-  const double eps = a.p.step_size;
+  const double eps = a.b.step_size_dev ? __ldg(a.b.step_size_dev) : a.p.step_size;
   const double delta_max = a.p.delta_max;
 
   extern __shared__ __align__(16) double smem[];

@@ -44,13 +44,16 @@ struct TileWriter {
   bool bulk;       // TMA path usable (alignment / size multiple of 16)
   int phase;
 
-  __device__ __forceinline__ void init(double* stage_, int n_, int nvalid_, const double* gbase) {
+  // gbase: the block's tile of stored iteration 0; iter_stride_bytes: distance between the tiles of consecutive stored
+  // iterations (C*n*8) — every tile address must be 16-byte aligned for the bulk path, not only the first
+  __device__ __forceinline__ void init(double* stage_, int n_, int nvalid_, const double* gbase, size_t iter_stride_bytes) {
     stage = stage_;
     n = n_;
     nvalid = nvalid_;
     phase = 0;
     const size_t bytes = (size_t)nvalid * n * sizeof(double);
-    bulk = ((bytes & 15) == 0) && ((((size_t)gbase) & 15) == 0) && (((size_t)n * BLOCK * 8) % 16 == 0);
+    bulk = ((bytes & 15) == 0) && ((((size_t)gbase) & 15) == 0) && (((size_t)n * BLOCK * 8) % 16 == 0) &&
+           ((iter_stride_bytes & 15) == 0);
   }
 
   // row: this thread's n doubles; gtile: global address of the block's tile for this iteration

@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kRwmhMinBlocks : 1) rwmh_kerne
   const int nvalid = (int)((C - chain0) < BLOCK ? (C - chain0) : BLOCK);
   const bool store = !(a.p.flags & MCMC_FLAG_NO_SAMPLES) && a.b.samples != nullptr;
   const bool injected = a.p.rng_mode == MCMC_RNG_INJECTED;
-  const double scale = a.p.step_size;
+  const double scale = a.b.step_size_dev ? __ldg(a.b.step_size_dev) : a.p.step_size;
 
   extern __shared__ __align__(16) double smem[];
   const int tabn = target_table_len(TID, n);
@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kRwmhMinBlocks : 1) rwmh_kerne
   __syncthreads();
 
   TileWriter<DS, BLOCK> tw;
-  if (store) tw.init(sm_stage, n, nvalid, a.b.samples + chain0 * n);
+  if (store) tw.init(sm_stage, n, nvalid, a.b.samples + chain0 * n, (size_t)C * n * sizeof(double));
 
   RngCtx rng;
   {
@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(BLOCK, MCMC_RWMH_WARP_MINBLOCKS) rwmh_warp_ker
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool store = !(a.p.flags & MCMC_FLAG_NO_SAMPLES) && a.b.samples != nullptr;
   const bool injected = a.p.rng_mode == MCMC_RNG_INJECTED;
-  const double scale = a.p.step_size;
+  const double scale = a.b.step_size_dev ? __ldg(a.b.step_size_dev) : a.p.step_size;
 
   extern __shared__ __align__(16) double smem[];
   const int tabn = target_table_len(TID, n);

@@ -81,7 +81,8 @@ def fused_sum(parts: Sequence[torch.Tensor]) -> list:
 
 def global_mean(local_sum: torch.Tensor, local_count: int) -> torch.Tensor:
     """sum_ranks(local_sum) / sum_ranks(local_count); the count rides in the same payload."""
-    cnt = torch.tensor([float(local_count)], dtype=torch.float64, device=local_sum.device)
+    # torch.full is a fill kernel; torch.tensor([...], device=cuda) would be a blocking H2D copy (a stream sync)
+    cnt = torch.full((1,), float(local_count), dtype=torch.float64, device=local_sum.device)
     s, c = fused_sum([local_sum, cnt])
     return s / c
 

@@ -65,12 +65,14 @@ def run_sampler(sampler: int, tag, init_position, *, key=0, step_size=0.0, num_s
                 inv_mass_matrix=None, gamma=0.0, steepness=1.0, schedule_id=0, track_proposals=False,
                 max_tree_depth=10, delta_max=1000.0, inject: Optional[dict] = None, welford=None,
                 welford_count=0.0, store_samples=True, chain_offset=0, device=None,
-                variant: Optional[str] = None) -> dict:
+                variant: Optional[str] = None, step_size_dev: Optional[torch.Tensor] = None) -> dict:
     """One *_run call on the device.  Returns a dict of CUDA tensors (reference shapes/dtypes).
 
     inject: dict(z=(T,C,D), u=(T,C)[, dir_u=(T,C,max_tree_depth), prop_u=...]) switches the kernels from
     the Philox stream to caller-supplied randomness (the parity tests' hook).
     welford: (mean (C,D), m2 (C,D)) CUDA tensors updated IN PLACE with every stored sample.
+    step_size_dev: 1-element float64 CUDA tensor the kernel reads epsilon from instead of `step_size` (device-resident
+    dual averaging: tuning.dual_averaging.DeviceDualAveraging).
     """
     if isinstance(init_position, torch.Tensor) and init_position.is_cuda and device is None:
         device = init_position.device
@@ -135,6 +137,10 @@ def run_sampler(sampler: int, tag, init_position, *, key=0, step_size=0.0, num_s
         assert tuple(wm.shape) == (Cn, D) and tuple(w2.shape) == (Cn, D)
         b.welford_mean, b.welford_m2 = _ptr(wm), _ptr(w2)
         b.welford_count = float(welford_count)
+    if step_size_dev is not None:
+        assert step_size_dev.is_cuda and step_size_dev.dtype == torch.float64 and step_size_dev.numel() >= 1
+        b.step_size_dev = _ptr(step_size_dev)
+        T["step_size_dev"] = step_size_dev
     ws_bytes = C.c_size_t(0)
     _abi.check(L.mcmc_workspace_bytes(int(sampler), C.byref(p), C.byref(ws_bytes)), variant)
     ws = None

@@ -23,7 +23,7 @@ from .. import _abi, dist
 from ..random import fold_in, split
 from ..runtime import _device, to_device, welford_sum_var
 from ..samplers.GRAHMC import _schedule_id, get_friction_schedule
-from .dual_averaging import da_init, da_reset, da_update, sample_batch
+from .dual_averaging import DeviceDualAveraging, da_init, da_reset, da_update, sample_batch
 
 
 
@@ -87,9 +87,14 @@ def run_adaptive_warmup(sampler: str, target_log_prob: Any, target_grad_log_prob
     steepness = (0.5 if schedule_type == "tanh" else 2.0) if grahmc else None
     sched_id = _schedule_id(get_friction_schedule(schedule_type or "constant")) if grahmc else 0
 
-    da_state = da_init(initial_step)
     position = _as_state_tensor(initial_position)
     dev = position.device
+    # On a CUDA device the dual-averaging state lives there too (DeviceDualAveraging): the sampler reads epsilon from
+    # device memory, the accept statistic goes kernel -> (all-reduce) -> da kernel, and nothing in the loop below waits
+    # for the GPU.  The host state machine (same formulas) drives the CPU stand-ins of the test suite.
+    on_device = position.is_cuda
+    da_dev = DeviceDualAveraging(initial_step, dev) if on_device else None
+    da_state = da_init(initial_step)
     inv_mass_matrix = None                                       # identity until the first window ends (:136)
     schedule = build_schedule(num_warmup)
     _log(verbose, f"Adaptation Schedule ({num_warmup} steps):")
@@ -104,6 +109,7 @@ def run_adaptive_warmup(sampler: str, target_log_prob: Any, target_grad_log_prob
     wf_count = 0.0
     n_batches_total = 0
     grad_evals = 0
+    grad_evals_dev = torch.zeros((), dtype=torch.int64, device=dev) if on_device else None
     for start_idx, end_idx, phase in schedule:
         window_len = end_idx - start_idx
         adapting = phase == "adaptation" and learn_mass_matrix
@@ -116,7 +122,7 @@ def run_adaptive_warmup(sampler: str, target_log_prob: Any, target_grad_log_prob
         samples_per_batch = window_len // num_batches
         for _ in range(num_batches):
             key, subkey = split(key)
-            current_step_size = math.exp(da_state.log_step)
+            current_step_size = 0.0 if on_device else math.exp(da_state.log_step)
             if adapting and wf_mean is None:
                 wf_mean = torch.zeros((n_chains, n_dim), dtype=torch.float64, device=dev)
                 wf_m2 = torch.zeros_like(wf_mean)
@@ -124,14 +130,23 @@ def run_adaptive_warmup(sampler: str, target_log_prob: Any, target_grad_log_prob
                                step_size=current_step_size, num_steps=num_steps, inv_mass_matrix=inv_mass_matrix,
                                gamma=gamma or 0.0, steepness=steepness or 1.0, schedule_id=sched_id,
                                max_tree_depth=max_tree_depth, welford=(wf_mean, wf_m2) if adapting else None,
-                               welford_count=wf_count, chain_offset=chain_offset)
+                               welford_count=wf_count, chain_offset=chain_offset,
+                               **({"step_size_dev": da_dev.step_dev} if on_device else {}))
             position = out["final_q"]
             if adapting:
                 wf_count += samples_per_batch
-            avg_accept = dist.mean_accept(out["accept_sum"], out["accept_terms"])   # :217-219
-            da_state = da_update(da_state, avg_accept, target_accept)
+            if on_device:
+                # sum over ranks on the sampler's stream, then the one-thread da_update kernel (:217-219)
+                # (the term count rides in the same payload: shards may differ in size by one chain)
+                acc = torch.cat([out["accept_sum"].reshape(1),
+                                 torch.full((1,), float(out["accept_terms"]), dtype=torch.float64, device=dev)])
+                da_dev.update(dist.all_reduce_sum_(acc), 0.0, target_accept)
+                grad_evals_dev += out["counters"][1]
+            else:
+                avg_accept = dist.mean_accept(out["accept_sum"], out["accept_terms"])   # :217-219
+                da_state = da_update(da_state, avg_accept, target_accept)
+                grad_evals += int(out["counters"][1].item())
             n_batches_total += 1
-            grad_evals += int(out["counters"][1].item())
         if adapting:
             # mean over ALL chains of the per-chain variances, shrunk towards 1 (:238-265)
             local = welford_sum_var(wf_m2, wf_count)
@@ -142,12 +157,19 @@ def run_adaptive_warmup(sampler: str, target_log_prob: Any, target_grad_log_prob
             variance = shrinkage_weight * variance + prior_weight * 1.0
             variance = torch.clamp(variance, min=1e-8)
             inv_mass_matrix = variance
-            _log(verbose, f"  Window finished. Updated Mass Matrix. Range: "
-                          f"[{float(variance.min()):.4f}, {float(variance.max()):.4f}]")
-            _log(verbose, f"    (n_samples_per_chain={n_samples:.0f}, n_chains={n_chains * dist.world_size()}, "
-                          f"shrinkage={shrinkage_weight:.3f})")
-            da_state = da_reset(da_state)                        # :272-273
+            if verbose:      # reading the range synchronises: only when someone is watching
+                _log(verbose, f"  Window finished. Updated Mass Matrix. Range: "
+                              f"[{float(variance.min()):.4f}, {float(variance.max()):.4f}]")
+                _log(verbose, f"    (n_samples_per_chain={n_samples:.0f}, n_chains={n_chains * dist.world_size()}, "
+                              f"shrinkage={shrinkage_weight:.3f})")
+            if on_device:
+                da_dev.reset()                                   # :272-273
+            else:
+                da_state = da_reset(da_state)
 
+    if on_device:
+        da_state = da_dev.to_host()                              # the first (and only) wait for the GPU
+        grad_evals = int(grad_evals_dev.item())
     final_step_size = float(math.exp(da_state.log_step_bar))
     _log(verbose, f"Warmup Complete. Final step_size: {final_step_size:.5f}")
     if inv_mass_matrix is None:

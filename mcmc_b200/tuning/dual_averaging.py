@@ -63,6 +63,46 @@ def da_reset(state: DualAveragingState) -> DualAveragingState:
                               omega=state.omega, t0=state.t0, kappa=state.kappa)
 
 
+class DeviceDualAveraging:
+    """The same state machine (da_init / da_update / da_reset) held in a float64[8] CUDA tensor and advanced by
+    one-thread kernels (mcmc_da_init / mcmc_da_update / mcmc_da_reset): the sampler reads epsilon from `step_dev`
+    (element 5) and the accept statistic never visits the host, so a whole warmup is enqueued without a sync."""
+
+    def __init__(self, initial_step_size: float, device, omega: float = 0.05, t0: float = 10.0, kappa: float = 0.75):
+        import ctypes as C
+        self._C = C
+        self.omega, self.t0, self.kappa = float(omega), float(t0), float(kappa)
+        self.state = torch.empty((8,), dtype=torch.float64, device=device)
+        self._L = _abi.lib()
+        _abi.check(self._L.mcmc_set_device(self.state.device.index))
+        _abi.check(self._L.mcmc_da_init(C.c_void_p(self.state.data_ptr()), float(initial_step_size), self._stream()))
+
+    def _stream(self):
+        return self._C.c_void_p(torch.cuda.current_stream(self.state.device).cuda_stream)
+
+    @property
+    def step_dev(self) -> torch.Tensor:
+        return self.state[5:6]
+
+    def update(self, accept_sum: torch.Tensor, n_terms: float, target_accept: float) -> None:
+        """accept_sum: 1-element float64 CUDA tensor (already summed over the ranks)."""
+        a = accept_sum.reshape(-1)
+        assert a.is_cuda and a.dtype == torch.float64
+        _abi.check(self._L.mcmc_da_update(self._C.c_void_p(self.state.data_ptr()), self._C.c_void_p(a.data_ptr()),
+                                          float(n_terms), float(target_accept), self.omega, self.t0, self.kappa,
+                                          self._stream()))
+        a.record_stream(torch.cuda.current_stream(self.state.device))
+
+    def reset(self) -> None:
+        _abi.check(self._L.mcmc_da_reset(self._C.c_void_p(self.state.data_ptr()), self._stream()))
+
+    def to_host(self) -> DualAveragingState:
+        """Synchronises: the host view of the state."""
+        v = self.state.cpu().numpy()
+        return DualAveragingState(log_step=float(v[0]), log_step_bar=float(v[1]), H_bar=float(v[2]), mu=float(v[3]),
+                                  count=int(v[4]), omega=self.omega, t0=self.t0, kappa=self.kappa)
+
+
 # ------------------------------------------------------------------ joint (step, gamma) dual averaging
 class JointDualAveragingState(NamedTuple):
     """tuning/dual_averaging.py:608-617."""
@@ -98,7 +138,7 @@ def joint_da_update(state: JointDualAveragingState, accept_stat: float, target_a
 def sample_batch(sampler: int, log_prob_fn, position, key, num_samples: int, *, step_size: float, num_steps: int = 0,
                  inv_mass_matrix=None, gamma: float = 0.0, steepness: float = 1.0, schedule_id: int = 0,
                  max_tree_depth: int = 10, welford=None, welford_count: float = 0.0, store_samples: bool = False,
-                 track_proposals: bool = False, chain_offset: int = 0) -> dict:
+                 track_proposals: bool = False, chain_offset: int = 0, step_size_dev=None) -> dict:
     """One `*_run(..., burn_in=0)` call of a tuning loop.  Returns the sampler's output dict plus
     `accept_sum` (0-d float64 tensor: this shard's sum of the DA statistic) and `accept_terms`."""
     tag = resolve_log_prob(log_prob_fn)
@@ -107,7 +147,7 @@ def sample_batch(sampler: int, log_prob_fn, position, key, num_samples: int, *, 
                       num_samples=int(num_samples), burn_in=0, inv_mass_matrix=inv_mass_matrix, gamma=float(gamma),
                       steepness=float(steepness), schedule_id=int(schedule_id), max_tree_depth=int(max_tree_depth),
                       welford=welford, welford_count=welford_count, track_proposals=track_proposals,
-                      store_samples=bool(store_samples or nuts), chain_offset=chain_offset)
+                      store_samples=bool(store_samples or nuts), chain_offset=chain_offset, step_size_dev=step_size_dev)
     n_chains = out["final_q"].shape[0]
     if nuts:
         # NUTS adapts on the mean Metropolis acceptance probability of the trajectories

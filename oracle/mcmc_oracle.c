@@ -310,7 +310,7 @@ static void hmc_chain(const McmcParams* p, const McmcBuffers* b, int64_t c, int 
                       const double* s_tab, unsigned long long* n_accept_total) {
   const int D = p->n_dim, L = p->num_steps;
   const int64_t C = p->n_chains, S = p->num_samples, B = p->burn_in;
-  const double eps = p->step_size;
+  const double eps = b->step_size_dev ? *b->step_size_dev : p->step_size;
   const double half_eps = 0.5 * eps; /* HMC.py:119 `half*step_sz`, GRAHMC.py:193 */
   Target tg;
   make_target(p, b, &tg);
@@ -408,7 +408,7 @@ static int hmc_like_run(const McmcParams* p, const McmcBuffers* b, int friction)
   if (friction) {
     if (p->schedule_id < 0 || p->schedule_id >= MCMC_NUM_SCHEDULES) return MCMC_EINVAL;
     s_tab = (double*)malloc(sizeof(double) * (p->num_steps > 0 ? p->num_steps : 1));
-    oracle_friction_table(p->schedule_id, p->num_steps, p->step_size, p->gamma, p->steepness, s_tab, NULL);
+    oracle_friction_table(p->schedule_id, p->num_steps, b->step_size_dev ? *b->step_size_dev : p->step_size, p->gamma, p->steepness, s_tab, NULL);
   }
   unsigned long long tot = 0;
 #pragma omp parallel for schedule(static) reduction(+ : tot)
@@ -432,7 +432,7 @@ int oracle_grahmc_run(const McmcParams* p, const McmcBuffers* b) { return hmc_li
 static void rwmh_chain(const McmcParams* p, const McmcBuffers* b, int64_t c, unsigned long long* tot) {
   const int D = p->n_dim;
   const int64_t C = p->n_chains, S = p->num_samples, B = p->burn_in;
-  const double scale = p->step_size;
+  const double scale = b->step_size_dev ? *b->step_size_dev : p->step_size;
   Target tg;
   make_target(p, b, &tg);
   Rng rng = {p, b, c};
@@ -486,7 +486,7 @@ static double dotv(const double* a, const double* b, int D) {
 static void nuts_chain(const McmcParams* p, const McmcBuffers* b, int64_t c, unsigned long long cnt[4]) {
   const int D = p->n_dim;
   const int64_t C = p->n_chains, S = p->num_samples, B = p->burn_in;
-  const double eps = p->step_size;
+  const double eps = b->step_size_dev ? *b->step_size_dev : p->step_size;
   const int max_depth = p->max_tree_depth;
   Target tg;
   make_target(p, b, &tg);

@@ -23,6 +23,8 @@ perf)
     for t in standard_normal rosenbrock neals_funnel; do e=0.5; [ $t = rosenbrock ] && e=0.02; [ $t = neals_funnel ] && e=0.1
       timeout 300 python tools/perf_hmc.py --sampler nuts --target $t --samples 96 --Ls 1 --eps $e; done
   } > $O/perf_$TAG.jsonl 2>&1; cat $O/perf_$TAG.jsonl ;;
+diag)
+  timeout 600 python tools/diag_probe.py > $O/diag_probe_$TAG.txt 2>&1; echo "diag rc=$?"; cat $O/diag_probe_$TAG.txt ;;
 configs)
   timeout 1200 python tools/run_configs.py --configs 1,2,3,4,5 --out $O/configs_${TAG}_1gpu.jsonl > $O/configs_$TAG.log 2>&1; echo "configs rc=$?"; tail -25 $O/configs_$TAG.log ;;
 ncu)
