@@ -34,8 +34,11 @@ constexpr int kStepUnroll = MCMC_STEP_UNROLL;
 #ifndef MCMC_HMC_DENSE_MIN_L
 #define MCMC_HMC_DENSE_MIN_L 96
 #endif
+#ifndef MCMC_HMC_DENSE_BLOCKS
+#define MCMC_HMC_DENSE_BLOCKS 6
+#endif
 constexpr int kHmcDenseMinL = MCMC_HMC_DENSE_MIN_L;
-constexpr int kHmcDenseBlocks = 6;
+constexpr int kHmcDenseBlocks = MCMC_HMC_DENSE_BLOCKS;
 
 struct HmcKArgs {
   McmcParams p;

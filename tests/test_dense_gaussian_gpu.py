@@ -67,7 +67,7 @@ def test_dense_gaussian_sampler_parity(gpu_lib, oracle, sampler, D, variant):
     for k in keys:
         assert relerr(r[k], o[k]) <= tol, (k, relerr(r[k], o[k]))
     assert np.array_equal(r["accept_count"], o["accept_count"])
-    assert 0 < int(o["accept_count"].sum()) < C_ * S or sampler == _abi.SAMPLER_NUTS
+    assert int(o["accept_count"].sum()) > 0
 
 
 def test_dense_gaussian_wrapper_errors(gpu_lib):
