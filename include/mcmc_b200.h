@@ -212,6 +212,20 @@ int mcmc_friction_table(int schedule_id, int num_steps, double step_size, double
    welford_mean/m2 exactly as S sequential welford_update calls would. */
 int mcmc_welford_finalize(const double* welford_m2, double count, int64_t n_chains, int32_t n_dim,
                           double* out_sum_var, void* workspace, size_t workspace_bytes, void* stream);
+/* mcmc_welford_finalize_noalloc: NO COUNTERPART IN THE REFERENCE — added for
+   callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
+   cudaMalloc).  Same result as mcmc_welford_finalize (same kernels, same order of operations: bit-identical), but the
+   256 x n_dim block partials live in a file-scope `static __device__` array of the library instead of a caller
+   workspace: 256 * MCMC_NOALLOC_MAX_DIM doubles = 256 KiB, held by every GPU that loads the library until exit.
+   The entry calls no cudaMalloc / cudaFree / allocating routine; inputs and outputs are the caller's device pointers
+   on the CURRENT device.  n_dim > MCMC_NOALLOC_MAX_DIM is rejected with MCMC_ENOTSUP.  The first call on each device
+   resolves the array's device address (cudaGetSymbolAddress): make one call per device outside a graph capture.
+   All calls on a device share the one array and it keeps the previous call's contents (none of it is read before it is
+   overwritten, so nothing needs clearing); two calls that OVERLAP on the GPU (different streams without an ordering
+   between them) race on it — serialise them or use mcmc_welford_finalize with separate workspaces. */
+#define MCMC_NOALLOC_MAX_DIM 128
+int mcmc_welford_finalize_noalloc(const double* welford_m2, double count, int64_t n_chains, int32_t n_dim,
+                                  double* out_sum_var, void* stream);
 int mcmc_chain_moments(const double* samples, int64_t num_samples, int64_t n_chains, int32_t n_dim,
                        double* welford_mean, double* welford_m2, double count_before, void* stream);
 /* Dual averaging on the device (tuning/dual_averaging.py:806-887: da_init / da_update / da_reset).  `state` is a DEVICE

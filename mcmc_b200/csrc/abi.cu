@@ -467,6 +467,52 @@ int mcmc_welford_finalize(const double* welford_m2, double count, int64_t n_chai
   return cuda_fail(cudaGetLastError(), "welford_finalize launch");
 }
 
+// ---- allocation-free variant of mcmc_welford_finalize (no counterpart in the reference; added for callers that cannot
+// allocate: CUDA graph capture, tight serving loops).  The block partials live in a file-scope device array instead of a
+// caller workspace.  In HOST code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the
+// address is resolved once per device with cudaGetSymbolAddress (that device current) and cached.
+static __device__ __align__(256) double g_noalloc_scratch[MCMC_REDUCE_BLOCKS * MCMC_NOALLOC_MAX_DIM];   // 256 KiB per GPU
+
+static std::mutex g_noalloc_mu;
+static double* g_noalloc_ptr[64] = {nullptr};
+
+// device address of g_noalloc_scratch on the CURRENT device (set-up on the first call per device)
+static int noalloc_scratch(double** out) {
+  int dev = 0;
+  if (int rc = cuda_fail(cudaGetDevice(&dev), "cudaGetDevice")) return rc;
+  if (dev < 0 || dev >= 64) { set_error("device ordinal %d outside [0, 64)", dev); return MCMC_ENOTSUP; }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    double* p = nullptr;
+    if (int rc = cuda_fail(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch), "cudaGetSymbolAddress(noalloc scratch)"))
+      return rc;
+    if (!p) { set_error("cudaGetSymbolAddress returned a null address"); return MCMC_ECUDA; }
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return MCMC_OK;
+}
+
+int mcmc_welford_finalize_noalloc(const double* welford_m2, double count, int64_t n_chains, int32_t n_dim,
+                                  double* out_sum_var, void* stream) {
+  if (!welford_m2 || !out_sum_var || n_dim < 1 || n_chains < 0) { set_error("bad argument"); return MCMC_EINVAL; }
+  if (n_dim > MCMC_NOALLOC_MAX_DIM) {
+    set_error("welford_finalize_noalloc: n_dim %d exceeds the static scratch (max %d dimensions = %zu bytes); use "
+              "mcmc_welford_finalize with a caller workspace", n_dim, MCMC_NOALLOC_MAX_DIM, sizeof(double) * MCMC_REDUCE_BLOCKS * MCMC_NOALLOC_MAX_DIM);
+    return MCMC_ENOTSUP;
+  }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  double* scratch = nullptr;
+  if (int rc = noalloc_scratch(&scratch)) return rc;
+  // nothing in the scratch has to start at zero: every one of the MCMC_REDUCE_BLOCKS blocks overwrites its n_dim partials
+  // (a block with no chains writes 0.0) before sum_partials reads exactly those MCMC_REDUCE_BLOCKS * n_dim values, so
+  // whatever an earlier call with another n_dim left behind is never read
+  const double n = count > 2.0 ? count : 2.0;
+  welford_finalize_kernel<<<MCMC_REDUCE_BLOCKS, 256, 0, (cudaStream_t)stream>>>(welford_m2, n - 1.0, n_chains, n_dim, scratch);
+  sum_partials_kernel<<<(n_dim + 127) / 128, 128, 0, (cudaStream_t)stream>>>(scratch, MCMC_REDUCE_BLOCKS, n_dim, out_sum_var);
+  return cuda_fail(cudaGetLastError(), "welford_finalize_noalloc launch");
+}
+
 int mcmc_chain_moments(const double* samples, int64_t num_samples, int64_t n_chains, int32_t n_dim, double* welford_mean,
                        double* welford_m2, double count_before, void* stream) {
   if (!samples || !welford_mean || !welford_m2) { set_error("null argument"); return MCMC_EINVAL; }
