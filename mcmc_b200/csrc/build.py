@@ -84,6 +84,34 @@ def build(variants=("fast", "strict"), verbose=False, jobs=None, extra_flags=(),
     return outs
 
 
+def build_xla_ffi(out_dir: str | None = None, include_dir: str | None = None, verbose: bool = False) -> str | None:
+    """Compiles mcmc_xla_ffi.cc (the jax.ffi custom-call handlers over the C ABI) into libmcmc_b200_xla_ffi.so, linked
+    against libmcmc_b200.so.  The XLA FFI header ships inside jaxlib: with `import jax` unavailable (this image) the
+    shim is SKIPPED with a message and None is returned — unless `include_dir` is given (any directory: without the
+    header in it the source compiles to its stub, which only exports mcmc_xla_ffi_available() == 0)."""
+    if include_dir is None:
+        try:
+            import jax  # noqa: F401
+            include_dir = jax.ffi.include_dir()
+        except Exception as e:
+            if verbose:
+                print(f"xla ffi shim skipped: jax is not importable ({type(e).__name__}); "
+                      "mcmc_b200/csrc/mcmc_xla_ffi.cc builds where jaxlib is installed", file=sys.stderr)
+            return None
+    out_dir = out_dir or HERE
+    out = os.path.join(out_dir, "libmcmc_b200_xla_ffi.so")
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", os.path.join(HERE, "mcmc_xla_ffi.cc"), "-I", include_dir,
+           "-I", "/usr/local/cuda/include", "-o", out]
+    main_lib = os.path.join(HERE, VARIANTS["fast"][1])
+    if os.path.exists(main_lib):
+        cmd += [main_lib, "-Wl,-rpath," + HERE]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"xla ffi shim failed to compile:\n{r.stdout}\n{r.stderr}")
+    return out
+
+
 if __name__ == "__main__":
     # python -m mcmc_b200.csrc.build [fast|strict ...] [--suffix _x -DFOO=1 ...]
     argv = sys.argv[1:]

@@ -103,15 +103,45 @@ def _check(out, o, off, n, exact, tol, keys_sc=("samples", "log_probs"), keys_c=
     assert np.array_equal(out["accept_count"][off:off + n].cpu().numpy(), o["accept_count"]), (what, off)
 
 
-def _yardstick(o, o1, floor, keys=("samples", "log_probs", "final_q", "final_lp", "final_g", "welford_mean", "welford_m2",
-                                    "mean_accept_probs")):
-    """The oracle's own response to a 1-ulp perturbation of the initial position, over every compared output (100x)."""
-    worst = 0.0
-    for k in keys:
-        if k in o and k in o1:
-            fin = np.isfinite(o[k]) & np.isfinite(o1[k])
-            worst = max(worst, relerr(np.where(fin, o1[k], 0.0), np.where(fin, o[k], 0.0)))
-    return max(floor, 100.0 * worst)
+def _per_chain_err(a, b, axis):
+    """max over everything but the chain axis of |a - b| / max(|b|, 1), where both are finite (inf/nan patterns must agree)."""
+    fin = np.isfinite(b)
+    with np.errstate(invalid="ignore"):
+        e = np.where(fin & np.isfinite(a), np.abs(a - b) / np.maximum(np.abs(b), 1.0), 0.0)
+    e = np.moveaxis(e, axis, 0).reshape(e.shape[axis], -1).max(axis=1)
+    bad = np.moveaxis(np.isfinite(a) != fin, axis, 0).reshape(e.shape[0], -1).any(axis=1)
+    return e, bad
+
+
+def _check_fast(got, o, o1, floor, what, max_chaotic=0.10):
+    """Fast build vs oracle, chain by chain.  `got`: dict of arrays already cut to the slice; o / o1: the oracle on the
+    slice and on the slice with the initial position moved by one ulp.  A chain's tolerance is max(floor, 100 x its own
+    response to that ulp); chains whose response exceeds 1e-8 are chaotic over this run (no tolerance separates a
+    reordered sum from a wrong result there) and are left out — at most `max_chaotic` of the slice — while every other
+    chain must also reproduce its accept count exactly.  Returns the number of chains compared."""
+    n = o["accept_count"].shape[0]
+    sens = np.zeros(n)
+    err = np.zeros(n)
+    mism = np.zeros(n, dtype=bool)
+    for k, arr in got.items():
+        if k not in o or k == "accept_count":
+            continue
+        axis = 0 if k in ("final_q", "final_g", "final_lp", "welford_mean", "welford_m2") else 1   # the chain axis
+        s_k, _ = _per_chain_err(o1[k], o[k], axis)
+        e_k, b_k = _per_chain_err(arr, o[k], axis)
+        sens = np.maximum(sens, s_k)
+        err = np.maximum(err, e_k)
+        mism |= b_k
+    sens = np.maximum(sens, (o1["accept_count"] != o["accept_count"]) * 1.0)    # an ulp flipped a decision: chaotic
+    ok = sens <= 1e-8
+    assert ok.mean() >= 1.0 - max_chaotic, (what, "chaotic chains", int((~ok).sum()), n)
+    tol = np.maximum(floor, 100.0 * sens)
+    worst = np.argmax(np.where(ok, err / tol, 0.0))
+    assert np.all(err[ok] <= tol[ok]), (what, "chain", int(worst), err[worst], tol[worst])
+    assert not mism[ok].any(), (what, "finite pattern")
+    assert np.array_equal(got["accept_count"][ok], o["accept_count"][ok]), what
+    assert np.median(err) <= 100 * floor, (what, "median", float(np.median(err)))
+    return int(ok.sum())
 
 
 # ---------------------------------------------------------------------------------------------- config 2
@@ -155,11 +185,12 @@ def test_config2_hmc_rosenbrock_fast_build_slices(gpu_lib, oracle, L, eps, sprea
                           flags=_abi.FLAG_TRACK_PROPOSALS)
         q1 = q0.clone()
         q1[off:off + n] = torch.from_numpy(np.nextafter(q0[off:off + n].cpu().numpy(), np.inf)).cuda()
-        o1 = _oracle_slice(oracle, _abi.SAMPLER_HMC, "rosenbrock", [0.1], q1, off, n, key, S, B, L, eps, "fast", w=w)
-        yard = _yardstick(o, o1, tol)
-        assert yard < 1e-6, yard                     # the comparison must stay meaningful
-        _check(out, o, off, n, exact=False, tol=yard, what=f"fast L={L}",
-               keys_sc=("samples", "log_probs", "prop_q", "prop_lp", "delta_h", "pre_q"))
+        o1 = _oracle_slice(oracle, _abi.SAMPLER_HMC, "rosenbrock", [0.1], q1, off, n, key, S, B, L, eps, "fast", w=w,
+                           flags=_abi.FLAG_TRACK_PROPOSALS)
+        keys = ("samples", "log_probs", "prop_q", "prop_lp", "delta_h", "pre_q")
+        got = {k: out[k][:, off:off + n].cpu().numpy() for k in keys}
+        got.update({k: out[k][off:off + n].cpu().numpy() for k in ("final_q", "final_lp", "final_g", "accept_count")})
+        _check_fast(got, o, o1, tol, f"fast L={L} off={off}")
 
 
 # ---------------------------------------------------------------------------------------------- config 3 (one tuning batch)
@@ -185,11 +216,11 @@ def test_config3_grahmc_funnel_tuning_batch_slices(gpu_lib, oracle, sched, steep
         q1[off:off + n] = torch.from_numpy(np.nextafter(q0[off:off + n].cpu().numpy(), np.inf)).cuda()
         o1 = _oracle_slice(oracle, _abi.SAMPLER_GRAHMC, "neals_funnel", [], q1, off, n, key, S, 0, L, eps, "fast",
                            flags=fl, gamma=1.0, steepness=steep, schedule_id=_abi.SCHEDULE_IDS[sched])
-        yard = _yardstick(o, o1, 1e-10)              # 100 iterations on the funnel amplify an ulp to ~1e-9..1e-8
-        assert yard < 1e-5, yard
-        _check(out, o, off, n, exact=False, tol=yard, what=sched)
-        _close(wm[off:off + n].cpu().numpy(), o["welford_mean"], False, yard, (sched, "welford_mean", off))
-        _close(w2[off:off + n].cpu().numpy(), o["welford_m2"], False, yard, (sched, "welford_m2", off))
+        got = {k: out[k][off:off + n].cpu().numpy() for k in ("final_q", "final_lp", "final_g", "accept_count")}
+        got["welford_mean"] = wm[off:off + n].cpu().numpy()
+        got["welford_m2"] = w2[off:off + n].cpu().numpy()
+        # 100 iterations on the funnel: chains near the neck amplify an ulp beyond any tolerance (left out, <= 25%)
+        assert _check_fast(got, o, o1, 1e-10, f"{sched} off={off}", max_chaotic=0.25) >= 48
     assert int(out["counters"][0]) == int(out["accept_count"].sum())
 
 
@@ -236,17 +267,17 @@ def test_config5_nuts_65536_chains_slices(gpu_lib, oracle, tname, tpar, eps, var
     for off, n in _slices(C):
         o = _oracle_slice(oracle, _abi.SAMPLER_NUTS, tname, tpar, q0, off, n, key, S, B, 0, eps, variant, md=md)
         assert np.array_equal(out["tree_depths"][:, off:off + n].cpu().numpy(), o["tree_depths"]), (tname, off)
-        tol = 1e-10
-        if not exact:
-            q1 = q0.clone()
-            q1[off:off + n] = torch.from_numpy(np.nextafter(q0[off:off + n].cpu().numpy(), np.inf)).cuda()
-            o1 = _oracle_slice(oracle, _abi.SAMPLER_NUTS, tname, tpar, q1, off, n, key, S, B, 0, eps, variant, md=md)
-            if np.array_equal(o1["tree_depths"], o["tree_depths"]):
-                tol = _yardstick(o, o1, 1e-10)       # depth-10 trees (1023 steps) in the funnel's neck amplify an ulp
-            assert tol < 1e-5, tol
-        _check(out, o, off, n, exact=exact, tol=tol, what=f"nuts {tname}")
-        _close(out["mean_accept_probs"][:, off:off + n].cpu().numpy(), o["mean_accept_probs"], False, max(tol, 1e-10),
-               (tname, "mean_accept_probs", off))
+        if exact:
+            _check(out, o, off, n, exact=True, tol=0.0, what=f"nuts {tname}")
+            assert np.array_equal(out["mean_accept_probs"][:, off:off + n].cpu().numpy(), o["mean_accept_probs"])
+            continue
+        q1 = q0.clone()
+        q1[off:off + n] = torch.from_numpy(np.nextafter(q0[off:off + n].cpu().numpy(), np.inf)).cuda()
+        o1 = _oracle_slice(oracle, _abi.SAMPLER_NUTS, tname, tpar, q1, off, n, key, S, B, 0, eps, variant, md=md)
+        got = {k: out[k][:, off:off + n].cpu().numpy() for k in ("samples", "log_probs", "mean_accept_probs")}
+        got.update({k: out[k][off:off + n].cpu().numpy() for k in ("final_q", "final_lp", "final_g", "accept_count")})
+        # depth-10 trees (1023 steps) in the funnel's neck amplify an ulp: those chains are left out (<= 25%)
+        _check_fast(got, o, o1, 1e-10, f"nuts {tname} off={off}", max_chaotic=0.25)
     d = out["tree_depths"].to(torch.int64)
     assert int(out["counters"][1]) >= int(((1 << d) - 1).sum())       # burn-in transitions count too
     assert int(d.max()) <= md and int(d.min()) >= 1

@@ -10,6 +10,8 @@ case $s in
 tests)
   timeout 1500 python -m pytest tests -m gpu -q --maxfail=60 -p no:cacheprovider > $O/pytest_$TAG.log 2>&1; echo "pytest rc=$?" | tee -a $O/pytest_$TAG.log
   tail -5 $O/pytest_$TAG.log ;;
+zz)
+  timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -q -p no:cacheprovider > $O/pytest_zz_$TAG.log 2>&1; echo "zz alone rc=$?"; tail -3 $O/pytest_zz_$TAG.log ;;
 smoke)
   timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke_$TAG.log 2>&1; echo "smoke rc=$?"; tail -2 $O/smoke_$TAG.log ;;
 bench)
