@@ -257,6 +257,8 @@ def run_gpu_arm(args) -> None:
             os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT,ENV")
             os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
+        from mcmc_b200 import dist as _mdist
+        _mdist.warm_up(dev)          # NCCL's lazy channel set-up happens here, not inside a timed leg
     _abi.check(_abi.lib("fast").mcmc_set_device(local))
 
     target = rosenbrock(D, scale=0.1)

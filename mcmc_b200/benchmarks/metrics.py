@@ -88,10 +88,12 @@ def compute_sliced_w2(samples, target_name: str, dim: int, n_reference: int = 50
     share = (n_reference + w - 1) // w
     key, sub = split(key)
     if flat.shape[0] > share:
+        # choice without replacement (metrics.py:135), drawn ON the device: a keyed random permutation of the row indices
+        # (a CPU randperm over 16.8 M rows per rank cost more than the whole distance)
         k = as_key(sub)
-        g = torch.Generator(device="cpu")
-        g.manual_seed((int(k[0]) << 32 | int(k[1])) ^ (dist.rank() if distributed else 0))
-        idx = torch.randperm(flat.shape[0], generator=g)[:share].to(flat.device)     # choice without replacement
+        g = torch.Generator(device=flat.device)
+        g.manual_seed(((int(k[0]) << 32 | int(k[1])) ^ (dist.rank() if distributed else 0)) & 0x7FFFFFFFFFFFFFFF)
+        idx = torch.randperm(flat.shape[0], generator=g, device=flat.device)[:share]
         flat = flat[idx]
     if w > 1:
         flat = dist.gather_chains(flat)[:n_reference]

@@ -1,6 +1,13 @@
 // nuts_inst.cu — instantiates the NUTS kernels and the batched target evaluator of
 // ONE target (-DMCMC_TID=k).
+#include <cstdlib>
+
 #include "nuts_kernel.cuh"
+#if defined(MCMC_WITH_NUTS_QUAD) && !MCMC_IS_FAITHFUL
+// quad-of-lanes-per-chain experiment (measured slower: profiles/nuts_quad_ab_r02.txt); compiled only on request:
+// python -m mcmc_b200.csrc.build --suffix _quad -DMCMC_WITH_NUTS_QUAD, then taken with MCMC_NUTS_QUAD=1
+#include "nuts_quad_kernel.cuh"
+#endif
 
 #ifndef MCMC_TID
 #error "compile with -DMCMC_TID=<target id>"
@@ -58,7 +65,11 @@ int launch_target_eval<MCMC_TID>(const McmcParams& p, const double* cov_inv, con
 template <>
 int launch_nuts<MCMC_TID>(const Launch& l) {
   switch (l.p.n_dim) {
-    case 20: return launch_nuts_variant<MCMC_TID, 20, 32>(l);
+    case 20:
+#if defined(MCMC_WITH_NUTS_QUAD) && !MCMC_IS_FAITHFUL
+      if (getenv("MCMC_NUTS_QUAD")) return launch_nuts_quad<MCMC_TID>(l);
+#endif
+      return launch_nuts_variant<MCMC_TID, 20, 32>(l);
     case 10: return launch_nuts_variant<MCMC_TID, 10, 32>(l);
     default: return launch_nuts_variant<MCMC_TID, 0, 32>(l);
   }

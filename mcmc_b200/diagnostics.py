@@ -141,9 +141,9 @@ def _split_rows(col: torch.Tensor):
     return torch.cat([col[:n], col[S - n:]], dim=0).contiguous(), n
 
 
-def variable_diagnostics(col: torch.Tensor, max_lag: Optional[int] = None) -> Dict[str, float]:
-    """All statistics of ONE variable from its (S, C_all) draws: rank-normalised split R-hat,
-    bulk / tail / mean ESS, mean, sd (ddof=1), mcse_mean."""
+def _variable_device(col: torch.Tensor, max_lag: Optional[int] = None):
+    """Device phase of one variable: enqueues the sorts and kernels and returns (packed device tensor, n_lags, n) without
+    waiting for the GPU.  Layout of the packed tensor: see _variable_finish."""
     _require_cuda(col)
     S, Cn = col.shape
     if S < 4:
@@ -159,13 +159,12 @@ def variable_diagnostics(col: torch.Tensor, max_lag: Optional[int] = None) -> Di
     a_fold, s_fold = split_chain_stats(zf, n, n, 1)
     # tail ESS: indicators of the 5% / 95% quantiles of ALL draws
     if S == 2 * n:
-        pos = torch.tensor([0.05, 0.95], dtype=torch.float64, device=col.device) * (N - 1)
-        lo = pos.floor().long()
-        hi = torch.clamp(lo + 1, max=N - 1)
-        q = sorted_vals[lo] + (pos - lo.to(torch.float64)) * (sorted_vals[hi] - sorted_vals[lo])   # np.quantile 'linear'
+        lo = (int((N - 1) * 0.05), int((N - 1) * 0.95))                      # floor of q*(N-1): host integers, no sync
+        fr = ((N - 1) * 0.05 - lo[0], (N - 1) * 0.95 - lo[1])
+        q = [sorted_vals[lo[k]] + fr[k] * (sorted_vals[min(lo[k] + 1, N - 1)] - sorted_vals[lo[k]]) for k in range(2)]   # np.quantile 'linear'
     else:
-        q = torch.quantile(col.reshape(-1).to(torch.float64), torch.tensor([0.05, 0.95], dtype=torch.float64,
-                                                                           device=col.device))
+        qq = torch.quantile(col.reshape(-1).to(torch.float64), torch.tensor([0.05, 0.95], dtype=torch.float64).to(col.device, non_blocking=True))
+        q = [qq[0], qq[1]]
     tails = []
     for k in range(2):
         ind = (split <= q[k]).to(torch.float64)
@@ -175,8 +174,13 @@ def variable_diagnostics(col: torch.Tensor, max_lag: Optional[int] = None) -> Di
     flat = col.reshape(-1).to(torch.float64)
     mean = flat.mean()
     sd = flat.std(unbiased=True)
-    host = torch.cat([a_bulk, s_bulk, a_fold[:1], s_fold, tails[0][0], tails[0][1], tails[1][0], tails[1][1], a_raw,
-                      s_raw, mean.reshape(1), sd.reshape(1)]).cpu().numpy()
+    packed = torch.cat([a_bulk, s_bulk, a_fold[:1], s_fold, tails[0][0], tails[0][1], tails[1][0], tails[1][1], a_raw,
+                        s_raw, mean.reshape(1), sd.reshape(1)])
+    return packed, a_bulk.numel(), n
+
+
+def _variable_finish(host: np.ndarray, nl: int, n: int) -> Dict[str, float]:
+    """Host phase: R-hat and Geyer ESS from the reduced sums of one variable (ArviZ `_rhat`, `_ess`)."""
     o = 0
 
     def take(k):
@@ -184,7 +188,6 @@ def variable_diagnostics(col: torch.Tensor, max_lag: Optional[int] = None) -> Di
         v = host[o:o + k]
         o += k
         return v
-    nl = a_bulk.numel()
     ab, sb = take(nl), take(3)
     af, sf = take(1), take(3)
     at0, st0 = take(nl), take(3)
@@ -195,6 +198,13 @@ def variable_diagnostics(col: torch.Tensor, max_lag: Optional[int] = None) -> Di
     ess_mean = _ess_from(ar, sr, n)
     return {"rhat": rhat, "ess_bulk": _ess_from(ab, sb, n), "ess_tail": min(_ess_from(at0, st0, n), _ess_from(at1, st1, n)),
             "ess_mean": ess_mean, "mean": mean_h, "sd": sd_h, "mcse_mean": sd_h / math.sqrt(ess_mean)}
+
+
+def variable_diagnostics(col: torch.Tensor, max_lag: Optional[int] = None) -> Dict[str, float]:
+    """All statistics of ONE variable from its (S, C_all) draws: rank-normalised split R-hat,
+    bulk / tail / mean ESS, mean, sd (ddof=1), mcse_mean."""
+    packed, nl, n = _variable_device(col, max_lag)
+    return _variable_finish(packed.cpu().numpy(), nl, n)
 
 
 _KEYS = ("rhat", "ess_bulk", "ess_tail", "ess_mean", "mean", "sd", "mcse_mean")
@@ -213,9 +223,14 @@ def compute_diagnostics(samples: torch.Tensor, distributed: bool = False, max_la
     else:
         cols, dims = samples, list(range(D))
     local = torch.zeros((D, len(_KEYS)), dtype=torch.float64)
-    for j, d in enumerate(dims):
-        r = variable_diagnostics(cols[:, :, j], max_lag)
-        local[d] = torch.tensor([r[k] for k in _KEYS], dtype=torch.float64)
+    # every variable's device work is enqueued before the first result is read: ONE wait for the GPU, and the host's
+    # Geyer loops run after it instead of stalling the stream twenty times
+    pending = [_variable_device(cols[:, :, j], max_lag) for j in range(len(dims))]
+    if pending:
+        host = torch.stack([p[0] for p in pending]).cpu().numpy()
+        for j, d in enumerate(dims):
+            r = _variable_finish(host[j], pending[j][1], pending[j][2])
+            local[d] = torch.tensor([r[k] for k in _KEYS], dtype=torch.float64)
     if distributed and dist.world_size() > 1:
         t = local.to(samples.device)
         dist.all_reduce_sum_(t)          # every variable is filled by exactly one rank, zeros elsewhere

@@ -47,6 +47,29 @@ def chain_shard(total_chains: int) -> Tuple[int, int]:
     return off, n
 
 
+def warm_up(device=None, n_dim: int = 20) -> None:
+    """Issue every collective this package uses once, with the payload shapes of the warmup and the diagnostics, so that
+    NCCL's lazy set-up (communicator, per-peer point-to-point channels of the first all-to-all, algorithm selection per
+    payload size) happens here and not inside a measured or latency-sensitive call: on 8 GPUs the first all-to-all
+    alone took 8 s of channel set-up in round 1 (profiles/configs_r01f_8gpu.jsonl, first config-5 line)."""
+    if not (is_dist() and world_size() > 1):
+        return
+    w = world_size()
+    dev = device if device is not None else (torch.device("cuda", torch.cuda.current_device())
+                                             if td.get_backend() == "nccl" else torch.device("cpu"))
+    for n in (1, 2, n_dim + 1, n_dim * 7):
+        td.all_reduce(torch.zeros((n,), dtype=torch.float64, device=dev))
+    td.all_reduce(torch.zeros((1,), dtype=torch.float64, device=dev), op=td.ReduceOp.MAX)
+    x = torch.zeros((4, n_dim), dtype=torch.float64, device=dev)
+    td.all_gather([torch.empty_like(x) for _ in range(w)], x)
+    n1 = torch.zeros((1,), dtype=torch.int64, device=dev)
+    td.all_gather([torch.zeros_like(n1) for _ in range(w)], n1)
+    if td.get_backend() == "nccl":
+        td.all_to_all([torch.empty((8,), dtype=torch.float64, device=dev) for _ in range(w)],
+                      [torch.zeros((8,), dtype=torch.float64, device=dev) for _ in range(w)])
+        torch.cuda.synchronize(dev)
+
+
 def all_reduce_sum_(t: torch.Tensor) -> torch.Tensor:
     """In-place sum over ranks (identity without a process group)."""
     if is_dist() and world_size() > 1:
@@ -143,6 +166,7 @@ def chains_to_variables(samples: torch.Tensor):
         # send block j = my chains of rank j's variables, (S, Cl, dn_j) contiguous
         send = [samples[:, :, variable_shard(D, j, w)[0]:sum(variable_shard(D, j, w))].contiguous() for j in range(w)]
         recv = [torch.empty((S, Cl, dn), dtype=samples.dtype, device=samples.device) for _ in range(w)]
+        COUNTERS["all_to_all"] += 1
         td.all_to_all(recv, send)
     else:
         mine = samples.contiguous()

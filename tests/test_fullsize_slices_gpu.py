@@ -269,7 +269,8 @@ def test_config5_nuts_65536_chains_slices(gpu_lib, oracle, tname, tpar, eps, var
         assert np.array_equal(out["tree_depths"][:, off:off + n].cpu().numpy(), o["tree_depths"]), (tname, off)
         if exact:
             _check(out, o, off, n, exact=True, tol=0.0, what=f"nuts {tname}")
-            assert np.array_equal(out["mean_accept_probs"][:, off:off + n].cpu().numpy(), o["mean_accept_probs"])
+            # the Metropolis weights go through exp(): CUDA's and glibc's differ by an ulp, so not bit for bit
+            assert relerr(out["mean_accept_probs"][:, off:off + n].cpu().numpy(), o["mean_accept_probs"]) <= 1e-12
             continue
         q1 = q0.clone()
         q1[off:off + n] = torch.from_numpy(np.nextafter(q0[off:off + n].cpu().numpy(), np.inf)).cuda()

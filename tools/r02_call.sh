@@ -25,6 +25,32 @@ perf)
     for t in standard_normal rosenbrock neals_funnel; do e=0.5; [ $t = rosenbrock ] && e=0.02; [ $t = neals_funnel ] && e=0.1
       timeout 300 python tools/perf_hmc.py --sampler nuts --target $t --samples 96 --Ls 1 --eps $e; done
   } > $O/perf_$TAG.jsonl 2>&1; cat $O/perf_$TAG.jsonl ;;
+nutsq)
+  timeout 150 python -m pytest tests/test_parity_gpu.py -m gpu -q -x -k "nuts" --timeout 40 -p no:cacheprovider > $O/pytest_nutsq_$TAG.log 2>&1; echo "nuts parity rc=$?"; tail -5 $O/pytest_nutsq_$TAG.log
+  timeout 300 python -m pytest --timeout 60 tests/test_fullsize_slices_gpu.py tests/test_edge_cases_gpu.py tests/test_fullsize_gpu.py tests/test_abi_gpu.py tests/test_reference_golden_gpu.py tests/test_dense_gaussian_gpu.py -m gpu -q -k "nuts or NUTS or 3-0 or 3-20 or 3-10 or no_spin or golden or step_api" -p no:cacheprovider > $O/pytest_nutsq2_$TAG.log 2>&1; echo "nuts others rc=$?"; tail -8 $O/pytest_nutsq2_$TAG.log
+  { for v in quad thread; do for t in standard_normal rosenbrock neals_funnel; do e=0.5; [ $t = rosenbrock ] && e=0.02; [ $t = neals_funnel ] && e=0.1
+      echo "variant=$v"; if [ $v = thread ]; then export MCMC_NUTS_THREAD=1; else unset MCMC_NUTS_THREAD; fi
+      timeout 60 python tools/perf_hmc.py --sampler nuts --target $t --samples 96 --Ls 1 --eps $e; done; done; unset MCMC_NUTS_THREAD
+  } > $O/nuts_quad_ab_$TAG.txt 2>&1; cat $O/nuts_quad_ab_$TAG.txt ;;
+nutsp)
+  timeout 200 python -m pytest tests/test_parity_gpu.py -m gpu -q -x -k "nuts" --timeout 60 -p no:cacheprovider > $O/pytest_nutsp_$TAG.log 2>&1; echo "nuts parity rc=$?"; tail -3 $O/pytest_nutsp_$TAG.log
+  { for t in standard_normal rosenbrock neals_funnel; do e=0.5; [ $t = rosenbrock ] && e=0.02; [ $t = neals_funnel ] && e=0.1
+      timeout 100 python tools/perf_hmc.py --sampler nuts --target $t --samples 96 --Ls 1 --eps $e; done
+    timeout 150 python tools/nuts_latency_probe.py
+  } > $O/nuts_perf_$TAG.txt 2>&1; cat $O/nuts_perf_$TAG.txt ;;
+abmisc)
+  { echo "== dense mat-vec: scalar vs DMMA"; timeout 60 ./tools/micro/dense_dmma_ab.bin
+    for v in "" _d5; do echo "== hmc lib variant '$v'"; lib=$PWD/mcmc_b200/csrc/libmcmc_b200$v.so
+      MCMC_B200_LIB=$lib timeout 120 python tools/perf_hmc.py --samples 64 --Ls 48,64,96,128 --eps 0.02; done
+    for v in "" _rw5 _rw3; do echo "== rwmh lib variant '$v'"; lib=$PWD/mcmc_b200/csrc/libmcmc_b200$v.so; [ -f $lib ] || continue
+      MCMC_B200_LIB=$lib timeout 120 python tools/perf_hmc.py --sampler rwmh --target standard_normal --chains 4194304 --samples 64 --Ls 1 --eps 0.532; done
+  } > $O/abmisc_$TAG.txt 2>&1; cat $O/abmisc_$TAG.txt ;;
+nutschunk)
+  { for ch in 0 1 2 4 8; do for t in standard_normal rosenbrock neals_funnel; do e=0.5; [ $t = rosenbrock ] && e=0.02; [ $t = neals_funnel ] && e=0.1
+      echo "MCMC_NUTS_CHUNK=$ch"; MCMC_NUTS_CHUNK=$ch timeout 300 python tools/perf_hmc.py --sampler nuts --target $t --samples 96 --Ls 1 --eps $e; done; done
+  } > $O/nuts_chunk_$TAG.txt 2>&1; cat $O/nuts_chunk_$TAG.txt ;;
+slices)
+  timeout 900 python -m pytest tests/test_fullsize_slices_gpu.py tests/test_grid_search_gpu.py tests/test_diagnostics_gpu.py tests/test_quality_gpu.py -m gpu -q -p no:cacheprovider > $O/pytest_slices_$TAG.log 2>&1; echo "slices rc=$?"; tail -8 $O/pytest_slices_$TAG.log ;;
 diag)
   timeout 600 python tools/diag_probe.py > $O/diag_probe_$TAG.txt 2>&1; echo "diag rc=$?"; cat $O/diag_probe_$TAG.txt ;;
 configs)

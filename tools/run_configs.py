@@ -179,6 +179,7 @@ def main():
     if world > 1:
         import torch.distributed as td
         td.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.warm_up()
     want = {int(x) for x in a.configs.split(",")}
     if 1 in want and dist.rank() == 0:
         config1()
