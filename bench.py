@@ -42,11 +42,11 @@ INV_MASS = np.linspace(0.5, 2.0, D)  # a non-trivial diagonal M^-1 to exercise t
 SEED = (0, 0)
 # algorithmic fp64 flops of THIS kernel's formulation (FMA = 2), DESIGN.md "flop model"
 # dram__bytes_read.sum + dram__bytes_write.sum of one hmc_kernel launch at the bench shape (ncu --set full captures of
-# L=16 and L=128: 803.7 MB and 1011.9 MB, profiles/ncu_hmc_L{16,128}_r01e.txt; the L=128 launch is the 168-register
-# instantiation, whose register spills add ~245 MB of local-memory write-back) — a constant from the profile, not a live
+# L=16 and L=128 of round 2: 804.3 MB and 1049.3 MB, profiles/ncu_hmc_L{16,128}_r02c.txt; the L=128 launch is the 168-register
+# instantiation, whose register spills add ~290 MB of local-memory write-back) — a constant from the profile, not a live
 # measurement; the algorithmic bytes are the stored samples + log-probs, the initial state read and the final q / g written
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 907.8e6
-NCU_TRAFFIC_SOURCE = ("profiles/ncu_hmc_L16_r01e.txt (803.7 MB), profiles/ncu_hmc_L128_r01e.txt (1011.9 MB incl. spill write-back); "
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 926.8e6
+NCU_TRAFFIC_SOURCE = ("profiles/ncu_hmc_L16_r02c.txt (804.3 MB), profiles/ncu_hmc_L128_r02c.txt (1049.3 MB incl. spill write-back); "
                       "mean of the two launches")
 F_STEP = 231.0           # per leapfrog step of one 20-D rosenbrock chain: 80 integrator (2 DFMA/dim) + 151 gradient (75 DFMA + 1 DMUL)
 F_ITER = 190.0           # per MH iteration outside the trajectory (momentum scaling, two kinetic energies, value)
@@ -126,6 +126,16 @@ class ClockSampler(threading.Thread):
 # CPU arm: the oracle port of the reference (bench.py is one of the few places allowed to run it)
 
 _NATIVE = {}
+_JSON_FD = {"fd": None}     # the real stdout when fd 1 has been pointed at stderr (N > 1: NCCL logs to stdout)
+
+
+def emit_json(line: dict) -> None:
+    text = json.dumps(line) + "\n"
+    if _JSON_FD["fd"] is None:
+        sys.stdout.write(text)
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD["fd"], text.encode())
 
 
 def native_oracle():
@@ -255,7 +265,11 @@ def run_gpu_arm(args) -> None:
         if "NCCL_DEBUG" not in os.environ:
             os.environ["NCCL_DEBUG"] = "INFO"
             os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT,ENV")
-            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        # NCCL logs to the process's stdout (fd 1): keep a duplicate of the real stdout for the JSON line and point fd 1
+        # at stderr for the rest of the run
+        sys.stdout.flush()
+        _JSON_FD["fd"] = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
         from mcmc_b200 import dist as _mdist
         _mdist.warm_up(dev)          # NCCL's lazy channel set-up happens here, not inside a timed leg
@@ -469,7 +483,7 @@ def run_gpu_arm(args) -> None:
                                               f"{list(L_GRID)} ({r['seconds']:.1f} s)",
                                     "note": "reference JAX CPU path unavailable on this box (jax not installed); C "
                                             "restatement oracle/mcmc_oracle.c, OpenMP over chains, gcc " + r["flags"]}
-        print(json.dumps(line), flush=True)
+        emit_json(line)
     if world > 1:
         dist.destroy_process_group()
 

@@ -45,6 +45,14 @@ abmisc)
     for v in "" _rw5 _rw3; do echo "== rwmh lib variant '$v'"; lib=$PWD/mcmc_b200/csrc/libmcmc_b200$v.so; [ -f $lib ] || continue
       MCMC_B200_LIB=$lib timeout 120 python tools/perf_hmc.py --sampler rwmh --target standard_normal --chains 4194304 --samples 64 --Ls 1 --eps 0.532; done
   } > $O/abmisc_$TAG.txt 2>&1; cat $O/abmisc_$TAG.txt ;;
+multi)
+  N=$(nvidia-smi -L | wc -l); echo "GPUs: $N"
+  timeout 600 python -m pytest tests/test_multigpu_gpu.py tests/test_abi_gpu.py -m gpu -q --timeout 300 -p no:cacheprovider > $O/pytest_multi_$TAG.log 2>&1; echo "multi tests rc=$?"; tail -4 $O/pytest_multi_$TAG.log
+  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 > $O/bench_${TAG}_${N}gpu.json 2> $O/bench_${TAG}_${N}gpu.err; echo "bench rc=$?"; tail -c 2500 $O/bench_${TAG}_${N}gpu.json; grep -c "NCCL INFO" $O/bench_${TAG}_${N}gpu.err; grep -m3 "nranks\|NVLS\|Connected all" $O/bench_${TAG}_${N}gpu.err | cut -c1-200
+  timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --impl reference --gpus $N --steps 2 --warmup 1 > $O/bench_ref_${TAG}_${N}gpu.json 2> /dev/null; echo "ref rc=$?"; tail -c 700 $O/bench_ref_${TAG}_${N}gpu.json ;;
+multicfg)
+  N=$(nvidia-smi -L | wc -l)
+  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 tools/run_configs.py --configs 3,5 --c4-chains 4194304 --out $O/configs_${TAG}_${N}gpu.jsonl > $O/configs_${TAG}_${N}gpu.log 2>&1; echo "configs rc=$?"; grep "^{" $O/configs_${TAG}_${N}gpu.log | cut -c1-400 ;;
 nutschunk)
   { for ch in 0 1 2 4 8; do for t in standard_normal rosenbrock neals_funnel; do e=0.5; [ $t = rosenbrock ] && e=0.02; [ $t = neals_funnel ] && e=0.1
       echo "MCMC_NUTS_CHUNK=$ch"; MCMC_NUTS_CHUNK=$ch timeout 300 python tools/perf_hmc.py --sampler nuts --target $t --samples 96 --Ls 1 --eps $e; done; done
