@@ -80,7 +80,11 @@ enum {
   MCMC_TARGET_ROSENBROCK = 6,        /* targets.py:367-387; params[0]=scale (a = 1/scale^2) */
   MCMC_TARGET_GAUSSIAN_MIXTURE = 7,  /* targets.py:432-454; params[0]=separation */
   MCMC_TARGET_DENSE_GAUSSIAN = 8,    /* general x^T P x with P = buffers.cov_inv (D*D); params[0]=logdet(Sigma) */
-  MCMC_NUM_TARGETS = 9
+  MCMC_NUM_TARGETS = 9,              /* built-in targets */
+  /* 9 .. 16: user targets registered at run time (mcmc_register_user_target): value + gradient supplied as CUDA source,
+     compiled into the same kernels as one more per-target translation unit (mcmc_b200/custom.py) */
+  MCMC_TARGET_USER0 = 9,
+  MCMC_MAX_USER_TARGETS = 8
 };
 
 /* friction schedules: samplers/GRAHMC.py:113-119 registry order */
@@ -188,6 +192,12 @@ int mcmc_run_host(int sampler, const McmcParams* p, const McmcBuffers* host, int
 /* free the cached arena of mcmc_run_host */
 int mcmc_host_arena_release(void);
 
+/* Extension point for densities outside benchmarks/targets.py (the reference's *_run accept ANY jax-differentiable
+   log_prob_fn: HMC.py:223, README.md:51-52; here the density must exist as device code).  A plugin library — the sampler
+   translation units compiled with -DMCMC_TID=9 and the user's `mcmc_user_log_prob_grad` (mcmc_b200/custom.py drives nvcc) —
+   hands its four launchers (opaque C++ function pointers of this library's internal types) to this entry and receives the
+   target id to put into McmcParams.target_id (MCMC_TARGET_USER0 + slot), or a negative MCMC_E* code. */
+int mcmc_register_user_target(void* launch_hmc, void* launch_rwmh, void* launch_nuts, void* launch_eval);
 /* log p and grad log p of n points (device pointers; lp or grad may be NULL) */
 int mcmc_target_eval(const McmcParams* p, const double* cov_inv, const double* q,
                      int64_t n, double* lp, double* grad, void* stream);

@@ -32,9 +32,10 @@ class TargetDistribution(NamedTuple):
 class TaggedLogProb:
     """log_prob_fn stand-in carrying the kernel tag (target id + parameters)."""
 
-    def __init__(self, target_name: str, dim: int, params, cov_inv=None):
+    def __init__(self, target_name: str, dim: int, params, cov_inv=None, target_id=None):
         self.target_name = target_name
-        self.target_id = _abi.TARGET_IDS[target_name]
+        # target_id is given for user targets registered at run time (mcmc_b200/custom.py)
+        self.target_id = _abi.TARGET_IDS[target_name] if target_id is None else int(target_id)
         self.dim = int(dim)
         self.target_params = [float(x) for x in params]
         self.cov_inv = None if cov_inv is None else np.ascontiguousarray(cov_inv, dtype=np.float64)
@@ -62,8 +63,8 @@ def resolve_log_prob(log_prob_fn) -> TaggedLogProb:
         return tag
     raise NotImplementedError(
         "log_prob_fn must come from mcmc_b200.benchmarks.targets (its analytic log-density and gradient are "
-        "fused into the CUDA kernels); arbitrary Python callables cannot be compiled into the sm_100a path and "
-        "there is no CPU fallback")
+        "fused into the CUDA kernels) or from mcmc_b200.custom.compile_target (value + gradient supplied as CUDA "
+        "source); arbitrary Python callables cannot be compiled into the sm_100a path and there is no CPU fallback")
 
 
 def _normal_init(std):

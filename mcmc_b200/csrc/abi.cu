@@ -104,6 +104,20 @@ static const EvalFn kEval[MCMC_NUM_TARGETS] = {launch_target_eval<0>, launch_tar
                                                launch_target_eval<3>, launch_target_eval<4>, launch_target_eval<5>,
                                                launch_target_eval<6>, launch_target_eval<7>, launch_target_eval<8>};
 
+// user targets (ids MCMC_TARGET_USER0 ..): launchers handed over by a plugin library (mcmc_register_user_target)
+struct UserTarget { HmcFn hmc; RunFn rwmh; RunFn nuts; EvalFn eval; };
+static UserTarget g_user[MCMC_MAX_USER_TARGETS] = {};
+static int g_user_count = 0;
+static std::mutex g_user_mu;
+
+static bool target_known(int tid) {
+  return (tid >= 0 && tid < MCMC_NUM_TARGETS) || (tid >= MCMC_TARGET_USER0 && tid < MCMC_TARGET_USER0 + g_user_count);
+}
+static HmcFn hmc_fn(int tid) { return tid < MCMC_NUM_TARGETS ? kHmc[tid] : g_user[tid - MCMC_TARGET_USER0].hmc; }
+static RunFn rwmh_fn(int tid) { return tid < MCMC_NUM_TARGETS ? kRwmh[tid] : g_user[tid - MCMC_TARGET_USER0].rwmh; }
+static RunFn nuts_fn(int tid) { return tid < MCMC_NUM_TARGETS ? kNuts[tid] : g_user[tid - MCMC_TARGET_USER0].nuts; }
+static EvalFn eval_fn(int tid) { return tid < MCMC_NUM_TARGETS ? kEval[tid] : g_user[tid - MCMC_TARGET_USER0].eval; }
+
 static int have_device() {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }
@@ -113,7 +127,7 @@ static int have_device() {
 static int validate(const McmcParams* p, const McmcBuffers* b, int sampler) {
   if (!p || !b) { set_error("null params/buffers"); return MCMC_EINVAL; }
   if (p->abi_version != MCMC_ABI_VERSION) { set_error("abi_version %u != %d", p->abi_version, MCMC_ABI_VERSION); return MCMC_EINVAL; }
-  if (p->target_id < 0 || p->target_id >= MCMC_NUM_TARGETS) { set_error("Unknown target id %d", p->target_id); return MCMC_EINVAL; }
+  if (!target_known(p->target_id)) { set_error("Unknown target id %d", p->target_id); return MCMC_EINVAL; }
   if (p->n_dim < 1 || p->n_dim > MCMC_MAX_DIM) { set_error("n_dim %d outside [1, %d]", p->n_dim, MCMC_MAX_DIM); return MCMC_ENOTSUP; }
   if (p->n_chains < 0 || p->num_samples < 0 || p->burn_in < 0) { set_error("negative size"); return MCMC_EINVAL; }
   if (p->n_chains > 0 && !b->init_q) { set_error("init_q is NULL"); return MCMC_EINVAL; }
@@ -152,10 +166,10 @@ static int run_device(int sampler, const McmcParams* p, const McmcBuffers* b, cu
     if (int rc = cuda_fail(cudaMemsetAsync(b->counters, 0, 4 * sizeof(unsigned long long), stream), "memset counters"))
       return rc;
   switch (sampler) {
-    case MCMC_SAMPLER_HMC: return kHmc[p->target_id](l, false);
-    case MCMC_SAMPLER_GRAHMC: return kHmc[p->target_id](l, true);
-    case MCMC_SAMPLER_RWMH: return kRwmh[p->target_id](l);
-    case MCMC_SAMPLER_NUTS: return kNuts[p->target_id](l);
+    case MCMC_SAMPLER_HMC: return hmc_fn(p->target_id)(l, false);
+    case MCMC_SAMPLER_GRAHMC: return hmc_fn(p->target_id)(l, true);
+    case MCMC_SAMPLER_RWMH: return rwmh_fn(p->target_id)(l);
+    case MCMC_SAMPLER_NUTS: return nuts_fn(p->target_id)(l);
   }
   set_error("Unknown sampler: %d", sampler);  // ValueError, adaptation.py:212
   return MCMC_EINVAL;
@@ -382,6 +396,15 @@ int mcmc_set_device(int device) {
   return cuda_fail(cudaSetDevice(device), "cudaSetDevice");
 }
 
+int mcmc_register_user_target(void* launch_hmc, void* launch_rwmh, void* launch_nuts, void* launch_eval) {
+  if (!launch_hmc || !launch_rwmh || !launch_nuts || !launch_eval) { set_error("register_user_target: null launcher"); return MCMC_EINVAL; }
+  std::lock_guard<std::mutex> lk(g_user_mu);
+  if (g_user_count >= MCMC_MAX_USER_TARGETS) { set_error("at most %d user targets per process", MCMC_MAX_USER_TARGETS); return MCMC_ENOTSUP; }
+  g_user[g_user_count] = UserTarget{reinterpret_cast<HmcFn>(launch_hmc), reinterpret_cast<RunFn>(launch_rwmh),
+                                    reinterpret_cast<RunFn>(launch_nuts), reinterpret_cast<EvalFn>(launch_eval)};
+  return MCMC_TARGET_USER0 + g_user_count++;
+}
+
 int mcmc_workspace_bytes(int sampler, const McmcParams* p, size_t* bytes) {
   if (!p || !bytes) { set_error("null argument"); return MCMC_EINVAL; }
   *bytes = (sampler == MCMC_SAMPLER_NUTS) ? nuts_workspace_bytes(*p)
@@ -405,11 +428,11 @@ int mcmc_nuts_run(const McmcParams* p, const McmcBuffers* b, void* stream) {
 int mcmc_target_eval(const McmcParams* p, const double* cov_inv, const double* q, int64_t n, double* lp, double* grad,
                      void* stream) {
   if (!p || (!q && n > 0)) { set_error("null argument"); return MCMC_EINVAL; }
-  if (p->target_id < 0 || p->target_id >= MCMC_NUM_TARGETS) { set_error("Unknown target id %d", p->target_id); return MCMC_EINVAL; }
+  if (!target_known(p->target_id)) { set_error("Unknown target id %d", p->target_id); return MCMC_EINVAL; }
   if (p->n_dim < 1 || p->n_dim > MCMC_MAX_DIM) { set_error("n_dim %d outside [1, %d]", p->n_dim, MCMC_MAX_DIM); return MCMC_ENOTSUP; }
   if (p->target_id == MCMC_TARGET_DENSE_GAUSSIAN && (!cov_inv || p->n_dim > 64)) { set_error("dense_gaussian needs cov_inv, n_dim <= 64"); return MCMC_EINVAL; }
   if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
-  return kEval[p->target_id](*p, cov_inv, q, n, lp, grad, (cudaStream_t)stream);
+  return eval_fn(p->target_id)(*p, cov_inv, q, n, lp, grad, (cudaStream_t)stream);
 }
 
 int mcmc_philox_fill(const McmcParams* p, int64_t it_begin, int64_t n_it, double* z, double* log_u, void* stream) {

@@ -19,6 +19,7 @@
 #endif
 
 #define MCMC_DYN_MAXD MCMC_MAX_DIM
+#define MCMC_TARGET_USER_TID_ 9   // template id the sampler units of a user-target plugin are compiled with
 #define MCMC_MAX_STEPS 2048  // friction table lives in shared memory
 
 namespace mcmc {

@@ -25,10 +25,12 @@ int launch_hmc<MCMC_TID>(const Launch& l, bool friction) {
   }
 #endif
   switch (l.p.n_dim) {
+#ifndef MCMC_USER_GENERIC_ONLY   // a user plugin may compile only the runtime-D kernels (seconds instead of minutes)
     case 20:
       return friction ? launch_hmc_variant<MCMC_TID, 20, true, 64>(l) : launch_hmc_variant<MCMC_TID, 20, false, 64>(l);
     case 10:
       return friction ? launch_hmc_variant<MCMC_TID, 10, true, 64>(l) : launch_hmc_variant<MCMC_TID, 10, false, 64>(l);
+#endif
     default:
       return friction ? launch_hmc_variant<MCMC_TID, 0, true, 32>(l) : launch_hmc_variant<MCMC_TID, 0, false, 32>(l);
   }

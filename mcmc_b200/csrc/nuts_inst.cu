@@ -55,9 +55,12 @@ int launch_target_eval<MCMC_TID>(const McmcParams& p, const double* cov_inv, con
       return rc;                                                                                       \
     kern<<<grid, 128, smem, s>>>(t, n, q, npts, lp, grad);                                             \
   } while (0)
+#ifndef MCMC_USER_GENERIC_ONLY
   if (n == 20) MCMC_TE(20);
   else if (n == 10) MCMC_TE(10);
-  else MCMC_TE(0);
+  else
+#endif
+    MCMC_TE(0);
 #undef MCMC_TE
   return cuda_fail(cudaGetLastError(), "target_eval launch");
 }
@@ -65,12 +68,14 @@ int launch_target_eval<MCMC_TID>(const McmcParams& p, const double* cov_inv, con
 template <>
 int launch_nuts<MCMC_TID>(const Launch& l) {
   switch (l.p.n_dim) {
+#ifndef MCMC_USER_GENERIC_ONLY
     case 20:
 #if defined(MCMC_WITH_NUTS_QUAD) && !MCMC_IS_FAITHFUL
       if (getenv("MCMC_NUTS_QUAD")) return launch_nuts_quad<MCMC_TID>(l);
 #endif
       return launch_nuts_variant<MCMC_TID, 20, 32>(l);
     case 10: return launch_nuts_variant<MCMC_TID, 10, 32>(l);
+#endif
     default: return launch_nuts_variant<MCMC_TID, 0, 32>(l);
   }
 }

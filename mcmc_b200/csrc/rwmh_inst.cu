@@ -18,8 +18,10 @@ int launch_rwmh<MCMC_TID>(const Launch& l) {
   const bool misaligned = (reinterpret_cast<uintptr_t>(l.b.samples) & 15u) != 0;
   const bool unrolled = misaligned || getenv("MCMC_RWMH_UNROLLED") != nullptr;
   switch (l.p.n_dim) {
+#ifndef MCMC_USER_GENERIC_ONLY
     case 20: return unrolled ? launch_rwmh_variant<MCMC_TID, 20, 128>(l) : launch_rwmh_warp_variant<MCMC_TID, 20, 128>(l);
     case 10: return unrolled ? launch_rwmh_variant<MCMC_TID, 10, 128>(l) : launch_rwmh_warp_variant<MCMC_TID, 10, 128>(l);
+#endif
     default: return launch_rwmh_variant<MCMC_TID, 0, 32>(l);
   }
 }

@@ -13,6 +13,14 @@
 #pragma once
 #include "common.cuh"
 
+// A user target (mcmc_b200/custom.py): the header defines, in the global namespace,
+//   __device__ double mcmc_user_log_prob_grad(const double* q, double* g, int n, const double* par);
+// returning log p(q) and writing grad log p(q) to g[0..n) (par = McmcParams.target_params).
+#define MCMC_TARGET_USER_TID 9
+#ifdef MCMC_USER_TARGET_HEADER
+#include MCMC_USER_TARGET_HEADER
+#endif
+
 namespace mcmc {
 
 // Host-derived scalar constants of one target (kernel parameter, constant bank).
@@ -265,6 +273,15 @@ __device__ __forceinline__ double target_eval(const TargetCtx& t, const int n_rt
       const double lp0 = t.c[1] + mx + log(es) - t.c[2];
       lp = lp0 + -0.5 * (s + t.c[3]);
     }
+#ifdef MCMC_USER_TARGET_HEADER
+  } else if (TID == MCMC_TARGET_USER_TID) {
+    if (WANT_G) {
+      lp = mcmc_user_log_prob_grad(q, g, n, t.par);
+    } else {
+      double gl[DS > 0 ? DS : MCMC_DYN_MAXD];   // value-only callers (RWMH): the gradient stores are dead code
+      lp = mcmc_user_log_prob_grad(q, gl, n, t.par);
+    }
+#endif
   } else if (TID == MCMC_TARGET_DENSE_GAUSSIAN) {
     // y = x P and yt = P x from the shared copy of P (broadcast reads); maha = y.x
     double maha = 0.0;
