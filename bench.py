@@ -262,7 +262,8 @@ def run_gpu_arm(args) -> None:
     if world > 1:
         # NCCL's INFO log (communicator ranks, NVLS / ring setup) goes to stderr; stdout carries rank 0's ONE JSON line.
         # A value the launcher already exported is respected.
-        if "NCCL_DEBUG" not in os.environ:
+        # (the GPU boxes export NCCL_DEBUG=VERSION: only the banner; anything else a launcher set is respected)
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() in ("", "VERSION"):
             os.environ["NCCL_DEBUG"] = "INFO"
             os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT,ENV")
         # NCCL logs to the process's stdout (fd 1): keep a duplicate of the real stdout for the JSON line and point fd 1
