@@ -37,6 +37,13 @@ constexpr int kStepUnroll = MCMC_STEP_UNROLL;
 #ifndef MCMC_HMC_DENSE_BLOCKS
 #define MCMC_HMC_DENSE_BLOCKS 6
 #endif
+// pairs per stage-interleaved draw batch (philox.cuh; 0: the pair-after-pair draw; must divide DS/2, else the whole row is
+// one batch).  Measured at the bench shape (profiles/draw_batch_ab_r02.txt): 0 / 2 / 5 / 10 give the same times at every L —
+// the per-iteration part of this kernel is not bound by the draw's instruction scheduling — so the default stays 0.
+#ifndef MCMC_HMC_DRAW_BATCH
+#define MCMC_HMC_DRAW_BATCH 0
+#endif
+constexpr int kHmcDrawBatch = MCMC_HMC_DRAW_BATCH;
 constexpr int kHmcDenseMinL = MCMC_HMC_DENSE_MIN_L;
 constexpr int kHmcDenseBlocks = MCMC_HMC_DENSE_BLOCKS;
 
@@ -256,6 +263,17 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
       const double* zsrc = a.b.z_inject + ((size_t)it * C + chain) * n;
 #pragma unroll
       for (int d = 0; d < n; ++d) p[d] = zsrc[d];
+    } else if (DS > 0 && DS % 2 == 0 && kHmcDrawBatch > 0) {
+      // all DS/2 Philox blocks and Box-Muller pairs advanced stage by stage (philox.cuh): same bits, shorter stalls
+      constexpr int kPairs = DS > 0 ? DS / 2 : 1;
+      constexpr int kNB = (kHmcDrawBatch > 0 && kPairs % kHmcDrawBatch == 0) ? kHmcDrawBatch : kPairs;
+#pragma unroll
+      for (int j0 = 0; j0 < kPairs; j0 += kNB) {
+        double zb[2 * kNB];
+        philox_normals_batch<kNB>(rng, (uint32_t)it, (uint32_t)j0, zb);
+#pragma unroll
+        for (int k = 0; k < 2 * kNB; ++k) p[2 * j0 + k] = zb[k];
+      }
     } else {
 #pragma unroll
       for (int j = 0; 2 * j < n; ++j) {

@@ -133,6 +133,12 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kRwmhMinBlocks : 1) rwmh_kerne
 #define MCMC_RWMH_WARP_MINBLOCKS 4
 #endif
 constexpr int kRwmhDrawUnroll = MCMC_RWMH_DRAW_UNROLL;
+// pairs per stage-interleaved draw batch (philox.cuh); measured at 4 M chains (profiles/draw_batch_ab_r02.txt):
+// 0 -> 2.93 TB/s, 2 -> 3.08, 5 -> 2.95, 10 -> 2.85
+#ifndef MCMC_RWMH_DRAW_BATCH
+#define MCMC_RWMH_DRAW_BATCH 2
+#endif
+constexpr int kRwmhDrawBatch = MCMC_RWMH_DRAW_BATCH;
 
 template <int TID, int DS, int BLOCK>
 __global__ void __launch_bounds__(BLOCK, MCMC_RWMH_WARP_MINBLOCKS) rwmh_warp_kernel(const RwmhKArgs a) {
@@ -184,6 +190,20 @@ __global__ void __launch_bounds__(BLOCK, MCMC_RWMH_WARP_MINBLOCKS) rwmh_warp_ker
     const int64_t si = it - B;
     // proposal = position + scale * noise (RWMH.py:98-99), pair by pair
     const double* zsrc = injected ? a.b.z_inject + ((size_t)it * C + chain) * n : nullptr;
+    if (!injected && kRwmhDrawBatch > 0 && (n / 2) % kRwmhDrawBatch == 0) {
+      // stage-interleaved draw of kRwmhDrawBatch pairs at a time (philox.cuh: same bits as the pair-after-pair loop)
+#pragma unroll
+      for (int j0 = 0; j0 < n / 2; j0 += kRwmhDrawBatch) {
+        double zb[2 * (kRwmhDrawBatch > 0 ? kRwmhDrawBatch : 1)];
+        philox_normals_batch<(kRwmhDrawBatch > 0 ? kRwmhDrawBatch : 1)>(rng, (uint32_t)it, (uint32_t)j0, zb);
+#pragma unroll
+        for (int k = 0; k < kRwmhDrawBatch; ++k) {
+          const double2 qq = *reinterpret_cast<const double2*>(my_q + 2 * (j0 + k));
+          my_p[(2 * (j0 + k)) * 32] = qq.x + scale * zb[2 * k];
+          my_p[(2 * (j0 + k) + 1) * 32] = qq.y + scale * zb[2 * k + 1];
+        }
+      }
+    } else {
 #pragma unroll kRwmhDrawUnroll
     for (int j = 0; j < n / 2; ++j) {
       double z0, z1;
@@ -196,6 +216,7 @@ __global__ void __launch_bounds__(BLOCK, MCMC_RWMH_WARP_MINBLOCKS) rwmh_warp_ker
       const double2 qq = *reinterpret_cast<const double2*>(my_q + 2 * j);
       my_p[(2 * j) * 32] = qq.x + scale * z0;
       my_p[(2 * j + 1) * 32] = qq.y + scale * z1;
+    }
     }
 #pragma unroll
     for (int d = 0; d < n; ++d) qn[d] = my_p[d * 32];

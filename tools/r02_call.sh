@@ -53,6 +53,12 @@ multi)
 multicfg)
   N=$(nvidia-smi -L | wc -l)
   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 tools/run_configs.py --configs 3,5 --c4-chains 4194304 --out $O/configs_${TAG}_${N}gpu.jsonl > $O/configs_${TAG}_${N}gpu.log 2>&1; echo "configs rc=$?"; grep "^{" $O/configs_${TAG}_${N}gpu.log | cut -c1-400 ;;
+drawab)
+  timeout 300 python -m pytest tests/test_fullsize_slices_gpu.py tests/test_rng_gpu.py tests/test_parity_gpu.py -m gpu -q --timeout 120 -k "config2 or config4 or rng or native or hmc_parity or rwmh" -p no:cacheprovider > $O/pytest_draw_$TAG.log 2>&1; echo "draw tests rc=$?"; tail -3 $O/pytest_draw_$TAG.log
+  { for v in _b0 _b2 "" _b10; do lib=$PWD/mcmc_b200/csrc/libmcmc_b200$v.so; [ -f $lib ] || continue; echo "== draw batch variant '$v'"
+      MCMC_B200_LIB=$lib timeout 120 python tools/perf_hmc.py --samples 64 --Ls 16,32,64,128 --eps 0.02
+      MCMC_B200_LIB=$lib timeout 120 python tools/perf_hmc.py --sampler rwmh --target standard_normal --chains 4194304 --samples 64 --Ls 1 --eps 0.532; done
+  } > $O/drawab_$TAG.txt 2>&1; cat $O/drawab_$TAG.txt ;;
 nutschunk)
   { for ch in 0 1 2 4 8; do for t in standard_normal rosenbrock neals_funnel; do e=0.5; [ $t = rosenbrock ] && e=0.02; [ $t = neals_funnel ] && e=0.1
       echo "MCMC_NUTS_CHUNK=$ch"; MCMC_NUTS_CHUNK=$ch timeout 300 python tools/perf_hmc.py --sampler nuts --target $t --samples 96 --Ls 1 --eps $e; done; done
