@@ -44,6 +44,27 @@ constexpr int kStepUnroll = MCMC_STEP_UNROLL;
 #define MCMC_HMC_DRAW_BATCH 0
 #endif
 constexpr int kHmcDrawBatch = MCMC_HMC_DRAW_BATCH;
+// Two experiment switches, both OFF by default (profiles/hmc_kin_ab_r02.txt: neither pays).  MCMC_HMC_KIN_WAYS=4 keeps
+// four interleaved partial sums for the two kinetic energies of an iteration instead of D dependent DFMAs;
+// MCMC_HMC_EARLY_LOAD=1 issues the shared-memory loads of the current state before the momentum draw.  With 16 warps
+// per SM the other warps already cover those latencies: the sum over the L grid moved by +0.2% / +0.5%, and the early
+// load costs the standard normal 10% (registers held across the draw).
+#ifndef MCMC_HMC_KIN_WAYS
+#define MCMC_HMC_KIN_WAYS 1
+#endif
+constexpr int kHmcKinWays = MCMC_IS_FAITHFUL ? 1 : MCMC_HMC_KIN_WAYS;
+#ifndef MCMC_HMC_EARLY_LOAD
+#define MCMC_HMC_EARLY_LOAD 0
+#endif
+template <int W>
+__device__ __forceinline__ double kin_fold(const double (&k)[W]) {
+  if (W == 4) return (k[0] + k[1 % W]) + (k[2 % W] + k[3 % W]);
+  if (W == 2) return k[0] + k[1 % W];
+  double s = k[0];
+#pragma unroll
+  for (int i = 1; i < W; ++i) s += k[i];
+  return s;
+}
 constexpr int kHmcDenseMinL = MCMC_HMC_DENSE_MIN_L;
 constexpr int kHmcDenseBlocks = MCMC_HMC_DENSE_BLOCKS;
 
@@ -258,6 +279,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
     if (it == B) acc = 0;  // HMC.py:276-282
     const int64_t si = it - B;
 
+#if MCMC_HMC_EARLY_LOAD
+    load_row<DS>(q, my_q, n);
+#pragma unroll
+    for (int d = 0; d < n; ++d) g[d] = sm_g[d * BLOCK + tid];
+#endif
     // ---- momentum p0 = z / sqrt(w) (HMC.py:172), H0 (HMC.py:176-177)
     if (injected) {
       const double* zsrc = a.b.z_inject + ((size_t)it * C + chain) * n;
@@ -283,7 +309,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
         if (2 * j + 1 < n) p[2 * j + 1] = z1;
       }
     }
-    double kin = 0.0;
+    double kin0[kHmcKinWays] = {0.0};
 #pragma unroll
     for (int d = 0; d < n; ++d) {
 #if MCMC_IS_FAITHFUL
@@ -291,14 +317,16 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
 #else
       p[d] = p[d] * sm_sqw[d];
 #endif
-      kin += (p[d] * p[d]) * sm_w[d];
+      kin0[d % kHmcKinWays] += (p[d] * p[d]) * sm_w[d];
     }
-    const double H0 = -lp + 0.5 * kin;
+    const double H0 = -lp + 0.5 * kin_fold(kin0);
 
     // ---- trajectory from the current state (cached lp and g: no re-evaluation, HMC.py:179-192)
+#if !MCMC_HMC_EARLY_LOAD
     load_row<DS>(q, my_q, n);
 #pragma unroll
     for (int d = 0; d < n; ++d) g[d] = sm_g[d * BLOCK + tid];
+#endif
     double lpn = lp;
 #if MCMC_IS_FAITHFUL
     for (int i = 0; i < L; ++i) {
@@ -358,10 +386,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) hmc_kernel(const HmcKArgs a) {
 #endif
 
     // ---- p <- -p, H1 with the non-finite guard, MH test (HMC.py:194-207)
-    double kin1 = 0.0;
+    double kin1[kHmcKinWays] = {0.0};
 #pragma unroll
-    for (int d = 0; d < n; ++d) kin1 += (p[d] * p[d]) * sm_w[d];  // (-p)^2 == p^2
-    double H1 = -lpn + 0.5 * kin1;
+    for (int d = 0; d < n; ++d) kin1[d % kHmcKinWays] += (p[d] * p[d]) * sm_w[d];  // (-p)^2 == p^2
+    double H1 = -lpn + 0.5 * kin_fold(kin1);
     if (!isfinite(H1)) H1 = 1e10;
     const double log_alpha = H0 - H1;
     const double log_u = injected ? log(a.b.u_inject[(size_t)it * C + chain]) : philox_accept_log_uniform(rng, (uint32_t)it);

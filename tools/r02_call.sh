@@ -59,6 +59,12 @@ drawab)
       MCMC_B200_LIB=$lib timeout 120 python tools/perf_hmc.py --samples 64 --Ls 16,32,64,128 --eps 0.02
       MCMC_B200_LIB=$lib timeout 120 python tools/perf_hmc.py --sampler rwmh --target standard_normal --chains 4194304 --samples 64 --Ls 1 --eps 0.532; done
   } > $O/drawab_$TAG.txt 2>&1; cat $O/drawab_$TAG.txt ;;
+kinab)
+  { for v in "" _k4 _e1 _k4e1; do lib=$PWD/mcmc_b200/csrc/libmcmc_b200$v.so; [ -f $lib ] || continue; echo "== hmc variant '$v' (k = kinetic sum ways, e = early state load)"
+      MCMC_B200_LIB=$lib timeout 120 python tools/perf_hmc.py --samples 64 --Ls 16,32,64,128 --eps 0.02
+      MCMC_B200_LIB=$lib timeout 120 python tools/perf_hmc.py --target standard_normal --samples 64 --Ls 16 --eps 0.3
+      MCMC_B200_LIB=$lib timeout 120 python tools/perf_hmc.py --target dense_gaussian --samples 64 --Ls 16 --eps 0.1; done
+  } > $O/kinab_$TAG.txt 2>&1; cat $O/kinab_$TAG.txt ;;
 nutschunk)
   { for ch in 0 1 2 4 8; do for t in standard_normal rosenbrock neals_funnel; do e=0.5; [ $t = rosenbrock ] && e=0.02; [ $t = neals_funnel ] && e=0.1
       echo "MCMC_NUTS_CHUNK=$ch"; MCMC_NUTS_CHUNK=$ch timeout 300 python tools/perf_hmc.py --sampler nuts --target $t --samples 96 --Ls 1 --eps $e; done; done
