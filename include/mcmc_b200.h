@@ -195,12 +195,23 @@ int mcmc_host_arena_release(void);
 /* Extension point for densities outside benchmarks/targets.py (the reference's *_run accept ANY jax-differentiable
    log_prob_fn: HMC.py:223, README.md:51-52; here the density must exist as device code).  A plugin library — the sampler
    translation units compiled with -DMCMC_TID=9 and the user's `mcmc_user_log_prob_grad` (mcmc_b200/custom.py drives nvcc) —
-   hands its four launchers (opaque C++ function pointers of this library's internal types) to this entry and receives the
+   hands its five launchers (opaque C++ function pointers of this library's internal types) to this entry and receives the
    target id to put into McmcParams.target_id (MCMC_TARGET_USER0 + slot), or a negative MCMC_E* code. */
-int mcmc_register_user_target(void* launch_hmc, void* launch_rwmh, void* launch_nuts, void* launch_eval);
+int mcmc_register_user_target(void* launch_hmc, void* launch_rwmh, void* launch_nuts, void* launch_eval, void* launch_leapfrog);
 /* log p and grad log p of n points (device pointers; lp or grad may be NULL) */
 int mcmc_target_eval(const McmcParams* p, const double* cov_inv, const double* q,
                      int64_t n, double* lp, double* grad, void* stream);
+
+/* The trajectory alone: num_steps leapfrog steps from (q, momentum, log_prob, grad) for every chain (device pointers,
+   [C][D] rows / [C]; asynchronous on `stream`; no allocation).  friction == 0 replaces `leapfrog` (samplers/HMC.py:
+   85-134: half-kick, drift with the diagonal inverse mass, value_and_grad, half-kick), friction != 0 replaces
+   `_trajectory_with_schedule` (samplers/GRAHMC.py:215-261) over `_conformal_leapfrog_step` (:152-211) with
+   s_i = exp(-gamma(i eps) eps/2) from p->schedule_id / gamma / steepness.  Uses p->target_id, target_params, n_chains,
+   n_dim, num_steps, step_size.  inv_mass NULL = ones; log_prob NULL = 0 (only returned unchanged when num_steps == 0);
+   any output may be NULL or alias its input.  num_steps == 0 copies the inputs (a scan of length 0). */
+int mcmc_leapfrog(const McmcParams* p, int friction, const double* cov_inv, const double* inv_mass, const double* q,
+                  const double* momentum, const double* log_prob, const double* grad, double* q_out, double* momentum_out,
+                  double* log_prob_out, double* grad_out, void* stream);
 
 /* The native random stream as a callable (the draws the samplers make in-kernel; counter layout in
    mcmc_b200/csrc/philox.cuh and oracle/rng_common.h).  Replaces the reference's random.normal(k_momentum, (C, D)) /

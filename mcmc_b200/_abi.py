@@ -80,7 +80,7 @@ BUFFER_FIELDS = [f[0] for f in McmcBuffers._fields_ if f[1] is _P and f[0] != "w
 EXPORTS = [
     "mcmc_abi_version", "mcmc_build_info", "mcmc_last_error", "mcmc_device_count", "mcmc_set_device", "mcmc_workspace_bytes",
     "mcmc_hmc_run", "mcmc_grahmc_run", "mcmc_rwmh_run", "mcmc_nuts_run",
-    "mcmc_run_host", "mcmc_host_arena_release", "mcmc_register_user_target", "mcmc_target_eval", "mcmc_philox_fill", "mcmc_friction_table",
+    "mcmc_run_host", "mcmc_host_arena_release", "mcmc_register_user_target", "mcmc_target_eval", "mcmc_leapfrog", "mcmc_philox_fill", "mcmc_friction_table",
     "mcmc_welford_finalize", "mcmc_welford_finalize_noalloc", "mcmc_chain_moments", "mcmc_da_init", "mcmc_da_update", "mcmc_da_reset", "mcmc_sum_f64", "mcmc_fp64_peak_probe",
     "mcmc_rank_normalize", "mcmc_split_chain_stats_workspace", "mcmc_split_chain_stats",
 ]
@@ -128,7 +128,8 @@ def lib(variant: str | None = None) -> C.CDLL:
         getattr(L, name).argtypes = [C.POINTER(McmcParams), C.POINTER(McmcBuffers), _P]
     L.mcmc_run_host.argtypes = [C.c_int, C.POINTER(McmcParams), C.POINTER(McmcBuffers), C.c_int]
     L.mcmc_target_eval.argtypes = [C.POINTER(McmcParams), _P, _P, C.c_int64, _P, _P, _P]
-    L.mcmc_register_user_target.argtypes = [_P, _P, _P, _P]
+    L.mcmc_register_user_target.argtypes = [_P, _P, _P, _P, _P]
+    L.mcmc_leapfrog.argtypes = [C.POINTER(McmcParams), C.c_int] + [_P] * 11
     L.mcmc_philox_fill.argtypes = [C.POINTER(McmcParams), C.c_int64, C.c_int64, _P, _P, _P]
     L.mcmc_friction_table.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, _P, _P, _P]
     L.mcmc_welford_finalize.argtypes = [_P, C.c_double, C.c_int64, C.c_int32, _P, _P, C.c_size_t, _P]

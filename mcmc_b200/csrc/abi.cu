@@ -87,7 +87,8 @@ int device_sm_count() {
   template <> int launch_rwmh<T>(const Launch&);                                                       \
   template <> int launch_nuts<T>(const Launch&);                                                       \
   template <> int launch_target_eval<T>(const McmcParams&, const double*, const double*, int64_t,      \
-                                        double*, double*, cudaStream_t);
+                                        double*, double*, cudaStream_t);                              \
+  template <> int launch_leapfrog<T>(const McmcParams&, const LeapfrogIO&, bool, cudaStream_t);
 MCMC_DECL(0) MCMC_DECL(1) MCMC_DECL(2) MCMC_DECL(3) MCMC_DECL(4) MCMC_DECL(5) MCMC_DECL(6) MCMC_DECL(7) MCMC_DECL(8)
 #undef MCMC_DECL
 
@@ -104,8 +105,13 @@ static const EvalFn kEval[MCMC_NUM_TARGETS] = {launch_target_eval<0>, launch_tar
                                                launch_target_eval<3>, launch_target_eval<4>, launch_target_eval<5>,
                                                launch_target_eval<6>, launch_target_eval<7>, launch_target_eval<8>};
 
+typedef int (*LeapfrogFn)(const McmcParams&, const LeapfrogIO&, bool, cudaStream_t);
+static const LeapfrogFn kLeapfrog[MCMC_NUM_TARGETS] = {launch_leapfrog<0>, launch_leapfrog<1>, launch_leapfrog<2>,
+                                                       launch_leapfrog<3>, launch_leapfrog<4>, launch_leapfrog<5>,
+                                                       launch_leapfrog<6>, launch_leapfrog<7>, launch_leapfrog<8>};
+
 // user targets (ids MCMC_TARGET_USER0 ..): launchers handed over by a plugin library (mcmc_register_user_target)
-struct UserTarget { HmcFn hmc; RunFn rwmh; RunFn nuts; EvalFn eval; };
+struct UserTarget { HmcFn hmc; RunFn rwmh; RunFn nuts; EvalFn eval; LeapfrogFn leapfrog; };
 static UserTarget g_user[MCMC_MAX_USER_TARGETS] = {};
 static int g_user_count = 0;
 static std::mutex g_user_mu;
@@ -117,6 +123,7 @@ static HmcFn hmc_fn(int tid) { return tid < MCMC_NUM_TARGETS ? kHmc[tid] : g_use
 static RunFn rwmh_fn(int tid) { return tid < MCMC_NUM_TARGETS ? kRwmh[tid] : g_user[tid - MCMC_TARGET_USER0].rwmh; }
 static RunFn nuts_fn(int tid) { return tid < MCMC_NUM_TARGETS ? kNuts[tid] : g_user[tid - MCMC_TARGET_USER0].nuts; }
 static EvalFn eval_fn(int tid) { return tid < MCMC_NUM_TARGETS ? kEval[tid] : g_user[tid - MCMC_TARGET_USER0].eval; }
+static LeapfrogFn leapfrog_fn(int tid) { return tid < MCMC_NUM_TARGETS ? kLeapfrog[tid] : g_user[tid - MCMC_TARGET_USER0].leapfrog; }
 
 static int have_device() {
   int n = 0;
@@ -396,12 +403,13 @@ int mcmc_set_device(int device) {
   return cuda_fail(cudaSetDevice(device), "cudaSetDevice");
 }
 
-int mcmc_register_user_target(void* launch_hmc, void* launch_rwmh, void* launch_nuts, void* launch_eval) {
-  if (!launch_hmc || !launch_rwmh || !launch_nuts || !launch_eval) { set_error("register_user_target: null launcher"); return MCMC_EINVAL; }
+int mcmc_register_user_target(void* launch_hmc, void* launch_rwmh, void* launch_nuts, void* launch_eval, void* launch_leapfrog) {
+  if (!launch_hmc || !launch_rwmh || !launch_nuts || !launch_eval || !launch_leapfrog) { set_error("register_user_target: null launcher"); return MCMC_EINVAL; }
   std::lock_guard<std::mutex> lk(g_user_mu);
   if (g_user_count >= MCMC_MAX_USER_TARGETS) { set_error("at most %d user targets per process", MCMC_MAX_USER_TARGETS); return MCMC_ENOTSUP; }
   g_user[g_user_count] = UserTarget{reinterpret_cast<HmcFn>(launch_hmc), reinterpret_cast<RunFn>(launch_rwmh),
-                                    reinterpret_cast<RunFn>(launch_nuts), reinterpret_cast<EvalFn>(launch_eval)};
+                                    reinterpret_cast<RunFn>(launch_nuts), reinterpret_cast<EvalFn>(launch_eval),
+                                    reinterpret_cast<LeapfrogFn>(launch_leapfrog)};
   return MCMC_TARGET_USER0 + g_user_count++;
 }
 
@@ -433,6 +441,25 @@ int mcmc_target_eval(const McmcParams* p, const double* cov_inv, const double* q
   if (p->target_id == MCMC_TARGET_DENSE_GAUSSIAN && (!cov_inv || p->n_dim > 64)) { set_error("dense_gaussian needs cov_inv, n_dim <= 64"); return MCMC_EINVAL; }
   if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
   return eval_fn(p->target_id)(*p, cov_inv, q, n, lp, grad, (cudaStream_t)stream);
+}
+
+int mcmc_leapfrog(const McmcParams* p, int friction, const double* cov_inv, const double* inv_mass, const double* q,
+                  const double* momentum, const double* log_prob, const double* grad, double* q_out, double* momentum_out,
+                  double* log_prob_out, double* grad_out, void* stream) {
+  if (!p) { set_error("null params"); return MCMC_EINVAL; }
+  if (p->abi_version != MCMC_ABI_VERSION) { set_error("abi_version %u != %d", p->abi_version, MCMC_ABI_VERSION); return MCMC_EINVAL; }
+  if (!target_known(p->target_id)) { set_error("Unknown target id %d", p->target_id); return MCMC_EINVAL; }
+  if (p->n_dim < 1 || p->n_dim > MCMC_MAX_DIM) { set_error("n_dim %d outside [1, %d]", p->n_dim, MCMC_MAX_DIM); return MCMC_ENOTSUP; }
+  if (p->n_chains < 0) { set_error("negative size"); return MCMC_EINVAL; }
+  if (p->n_chains > 0 && (!q || !momentum || !grad)) { set_error("leapfrog: position, momentum and grad_log_prob are required"); return MCMC_EINVAL; }
+  if (p->num_steps < 0 || p->num_steps > MCMC_MAX_STEPS) { set_error("num_steps %d outside [0, %d]", p->num_steps, MCMC_MAX_STEPS); return MCMC_ENOTSUP; }
+  if (friction && (p->schedule_id < 0 || p->schedule_id >= MCMC_NUM_SCHEDULES)) {
+    set_error("Unknown friction schedule id %d", p->schedule_id); return MCMC_EINVAL;  // KeyError, GRAHMC.py:122
+  }
+  if (p->target_id == MCMC_TARGET_DENSE_GAUSSIAN && (!cov_inv || p->n_dim > 64)) { set_error("dense_gaussian needs cov_inv, n_dim <= 64"); return MCMC_EINVAL; }
+  if (have_device() == 0) { set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  const LeapfrogIO io{cov_inv, inv_mass, q, momentum, log_prob, grad, q_out, momentum_out, log_prob_out, grad_out};
+  return leapfrog_fn(p->target_id)(*p, io, friction != 0, (cudaStream_t)stream);
 }
 
 int mcmc_philox_fill(const McmcParams* p, int64_t it_begin, int64_t n_it, double* z, double* log_u, void* stream) {

@@ -74,6 +74,12 @@ template <int TID> int launch_rwmh(const Launch& l);
 template <int TID> int launch_nuts(const Launch& l);
 template <int TID> int launch_target_eval(const McmcParams& p, const double* cov_inv, const double* q,
                                           int64_t n, double* lp, double* grad, cudaStream_t s);
+// the trajectory alone (leapfrog_kernel.cuh): device pointers of mcmc_leapfrog, instantiated in hmc_inst.cu
+struct LeapfrogIO {
+  const double *cov_inv, *inv_mass, *q, *mom, *lp, *grad;
+  double *q_out, *mom_out, *lp_out, *grad_out;
+};
+template <int TID> int launch_leapfrog(const McmcParams& p, const LeapfrogIO& io, bool friction, cudaStream_t s);
 
 // workspace layouts (bytes), shared by the launchers and mcmc_workspace_bytes
 struct NutsWs {

@@ -1,6 +1,7 @@
 // hmc_inst.cu — instantiates the HMC/GRAHMC kernels of ONE target (-DMCMC_TID=k),
 // so the nine targets compile in parallel.
 #include "hmc_kernel.cuh"
+#include "leapfrog_kernel.cuh"
 #ifdef MCMC_WITH_WS
 // the warp-specialised variant (measured 4-6% slower, profiles/ncu_hmc_ws_r01.txt) is an experiment: compiled only with
 // -DMCMC_WITH_WS (python -m mcmc_b200.csrc.build --suffix _ws -DMCMC_WITH_WS) and then taken with MCMC_HMC_WS=1
@@ -34,6 +35,11 @@ int launch_hmc<MCMC_TID>(const Launch& l, bool friction) {
     default:
       return friction ? launch_hmc_variant<MCMC_TID, 0, true, 32>(l) : launch_hmc_variant<MCMC_TID, 0, false, 32>(l);
   }
+}
+
+template <>
+int launch_leapfrog<MCMC_TID>(const McmcParams& p, const LeapfrogIO& io, bool friction, cudaStream_t s) {
+  return launch_leapfrog_impl<MCMC_TID>(p, io, friction, s);
 }
 
 }  // namespace mcmc

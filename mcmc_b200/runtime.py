@@ -82,7 +82,7 @@ def run_sampler(sampler: int, tag, init_position, *, key=0, step_size=0.0, num_s
     q0, _ = ensure_batched(q0)
     q0 = q0.contiguous()
     Cn, D = q0.shape
-    if D != tag.dim:
+    if tag.dim and D != tag.dim:
         raise ValueError(f"init_position has n_dim={D} but the target was built with dim={tag.dim}")
     S, B = int(num_samples), int(burn_in)
     seed = as_key(key)
@@ -170,7 +170,7 @@ def target_eval(tag, x, want_grad=True, device=None, variant=None):
     single = xt.ndim == 1
     xt = xt.reshape(-1, xt.shape[-1]).contiguous()
     n, D = xt.shape
-    if D != tag.dim:
+    if tag.dim and D != tag.dim:
         raise ValueError(f"x has n_dim={D} but the target was built with dim={tag.dim}")
     lp = torch.empty((n,), dtype=torch.float64, device=dev)
     g = torch.empty((n, D), dtype=torch.float64, device=dev) if want_grad else None
@@ -181,6 +181,36 @@ def target_eval(tag, x, want_grad=True, device=None, variant=None):
     if single:
         return lp[0], (g[0] if g is not None else None)
     return lp, g
+
+
+def leapfrog(tag, position, momentum, log_prob, grad_log_prob, step_size, num_steps, inv_mass_matrix=None, *,
+             friction=False, gamma=0.0, steepness=1.0, schedule_id=0, device=None, variant=None):
+    """num_steps leapfrog steps for every chain on the device (mcmc_leapfrog: HMC.py:85-134; with friction GRAHMC.py:
+    215-261).  Returns (position, momentum, log_prob, grad_log_prob) as new CUDA float64 tensors."""
+    if isinstance(position, torch.Tensor) and position.is_cuda and device is None:
+        device = position.device
+    dev = _device(device)
+    L = _abi.lib(variant)
+    q = to_device(position, dev)
+    q, _ = ensure_batched(q)
+    q = q.contiguous()
+    Cn, D = q.shape
+    if tag.dim and D != tag.dim:
+        raise ValueError(f"position has n_dim={D} but the target was built with dim={tag.dim}")
+    mom = to_device(momentum, dev).reshape(Cn, D).contiguous()
+    g = to_device(grad_log_prob, dev).reshape(Cn, D).contiguous()
+    lp = to_device(log_prob, dev).reshape(Cn).contiguous()
+    w = to_device(inv_mass_matrix, dev)
+    if w is not None and tuple(w.shape) != (D,):
+        raise ValueError(f"inv_mass_matrix must have shape ({D},)")
+    p = make_params(tag.target_id, tag.target_params, Cn, D, 0, 0, int(num_steps), float(step_size), float(gamma),
+                    float(steepness), int(schedule_id))
+    qo, po, go, lo = torch.empty_like(q), torch.empty_like(mom), torch.empty_like(g), torch.empty_like(lp)
+    ci = to_device(tag.cov_inv, dev)
+    _abi.check(L.mcmc_set_device(dev.index), variant)
+    _abi.check(L.mcmc_leapfrog(C.byref(p), int(bool(friction)), _ptr(ci), _ptr(w), _ptr(q), _ptr(mom), _ptr(lp), _ptr(g),
+                               _ptr(qo), _ptr(po), _ptr(lo), _ptr(go), _stream_ptr(dev)), variant)
+    return qo, po, lo, go
 
 
 def philox_fill(key, n_chains: int, n_dim: int, it_begin: int, n_it: int, chain_offset: int = 0, device=None,

@@ -14,10 +14,15 @@ from typing import Callable, Dict, NamedTuple, Optional
 import torch
 
 from .. import _abi
-from ..benchmarks.targets import resolve_log_prob
+from ..benchmarks.targets import TaggedLogProb, resolve_log_prob
 from ..random import split
 from ..runtime import run_sampler
+from ..runtime import leapfrog as _leapfrog_device
 from .HMC import _pack, hmc_init
+
+
+# N(0, I) with its normaliser, for any dimension (samplers/GRAHMC.py:42-46): a tagged log_prob_fn like the factories'
+standard_normal_log_prob = TaggedLogProb("standard_normal", 0, [1.0])
 
 
 class RAHMCState(NamedTuple):
@@ -48,6 +53,11 @@ def sine_schedule(t, T, gamma_max, steepness=None):
     return gamma_max * math.sin(math.pi * (t / T - 0.5))
 
 
+def constant_schedule_default(t, T):
+    """Constant schedule with gamma = 1 (samplers/GRAHMC.py:108-110)."""
+    return constant_schedule(t, T, gamma=1.0, steepness=None)
+
+
 FRICTION_SCHEDULES: Dict[str, Callable] = {
     "constant": constant_schedule,
     "tanh": tanh_schedule,
@@ -73,6 +83,26 @@ def _schedule_id(friction_schedule) -> int:
     raise NotImplementedError(
         "friction_schedule must be one of mcmc_b200.samplers.GRAHMC.FRICTION_SCHEDULES (or its name); "
         "arbitrary Python schedules cannot be compiled into the kernel")
+
+
+def _conformal_leapfrog_step(position, momentum, step_size: float, gamma: float, log_prob, grad_log_prob, log_prob_fn,
+                             inv_mass_matrix, *, _variant: Optional[str] = None):
+    """One conformal leapfrog step with friction `gamma` (samplers/GRAHMC.py:152-211): (q, p, log_prob, grad_log_prob).
+    Runs as a one-step trajectory of the constant schedule, whose first half gives -gamma_max (GRAHMC.py:69-72)."""
+    tag = resolve_log_prob(log_prob_fn)
+    return _leapfrog_device(tag, position, momentum, log_prob, grad_log_prob, step_size, 1, inv_mass_matrix, friction=True,
+                            gamma=-float(gamma), steepness=1.0, schedule_id=_abi.SCHEDULE_IDS["constant"], variant=_variant)
+
+
+def _trajectory_with_schedule(position, momentum, step_size: float, gamma_max: float, steepness: float, log_prob,
+                              grad_log_prob, num_steps: int, log_prob_fn, friction_schedule, inv_mass_matrix, *,
+                              _variant: Optional[str] = None):
+    """A full leapfrog trajectory with time-dependent friction (samplers/GRAHMC.py:215-261), one kernel launch.
+    Returns (position, momentum, log_prob, grad_log_prob) — the reference's order for this function."""
+    tag = resolve_log_prob(log_prob_fn)
+    return _leapfrog_device(tag, position, momentum, log_prob, grad_log_prob, step_size, num_steps, inv_mass_matrix,
+                            friction=True, gamma=float(gamma_max), steepness=1.0 if steepness is None else float(steepness),
+                            schedule_id=_schedule_id(friction_schedule), variant=_variant)
 
 
 def rahmc_init(init_position, log_prob_fn) -> RAHMCState:

@@ -14,6 +14,7 @@ from .. import _abi
 from ..benchmarks.targets import resolve_log_prob
 from ..random import split
 from ..runtime import ensure_batched, run_sampler, target_eval, to_device, _device
+from ..runtime import leapfrog as _leapfrog_device
 
 
 class HMCState(NamedTuple):
@@ -30,6 +31,16 @@ def hmc_init(init_position, log_prob_fn) -> HMCState:
                                                              if getattr(init_position, "is_cuda", False) else None)))
     lp, g = target_eval(tag, pos, want_grad=True)
     return HMCState(pos, lp, g, torch.zeros(pos.shape[0], dtype=torch.int32, device=pos.device))
+
+
+def leapfrog(position, momentum, step_size: float, log_prob, grad_log_prob, log_prob_fn, num_steps: int, inv_mass_matrix,
+             *, _variant: Optional[str] = None):
+    """Leapfrog integration for every chain (samplers/HMC.py:85-134), one kernel launch (csrc/leapfrog_kernel.cuh).
+    Returns (final_position, final_momentum, final_grad_log_prob, final_log_prob) — the reference's order."""
+    tag = resolve_log_prob(log_prob_fn)
+    q, p, lp, g = _leapfrog_device(tag, position, momentum, log_prob, grad_log_prob, step_size, num_steps, inv_mass_matrix,
+                                   variant=_variant)
+    return q, p, g, lp
 
 
 def _pack(out, state_cls, track):

@@ -391,6 +391,53 @@ static void hmc_chain(const McmcParams* p, const McmcBuffers* b, int64_t c, int 
   *n_accept_total += (unsigned long long)acc;
 }
 
+/* The trajectory alone.  friction == 0: `leapfrog` (samplers/HMC.py:85-134: lf_step scanned num_steps times);
+   friction != 0: `_trajectory_with_schedule` (samplers/GRAHMC.py:215-261) over `_conformal_leapfrog_step` (:152-211).
+   Host pointers; lp may be NULL (taken as 0, only returned when num_steps == 0); outputs may be NULL. */
+int oracle_leapfrog(const McmcParams* p, int friction, const double* cov_inv, const double* inv_mass, const double* q,
+                    const double* mom, const double* lp, const double* grad, double* q_out, double* mom_out,
+                    double* lp_out, double* grad_out) {
+  if (!p || p->abi_version != MCMC_ABI_VERSION) return MCMC_EINVAL;
+  if (p->n_dim < 1 || p->n_dim > ORACLE_MAXD || p->num_steps < 0) return MCMC_EINVAL;
+  if (friction && (p->schedule_id < 0 || p->schedule_id >= MCMC_NUM_SCHEDULES)) return MCMC_EINVAL;
+  const int D = p->n_dim, L = p->num_steps;
+  const double eps = p->step_size, half_eps = 0.5 * eps; /* HMC.py:119 `half*step_sz`, GRAHMC.py:193 */
+  double* s_tab = NULL;
+  if (friction && L > 0) {
+    s_tab = (double*)malloc(sizeof(double) * (size_t)L);
+    if (!s_tab) return MCMC_ECUDA;
+    oracle_friction_table(p->schedule_id, L, eps, p->gamma, p->steepness, s_tab, NULL);
+  }
+  McmcBuffers bb;
+  memset(&bb, 0, sizeof(bb));
+  bb.cov_inv = cov_inv;
+  Target tg;
+  make_target(p, &bb, &tg);
+#pragma omp parallel for schedule(static)
+  for (int64_t c = 0; c < p->n_chains; ++c) {
+    double w[ORACLE_MAXD], qn[ORACLE_MAXD], pn[ORACLE_MAXD], gn[ORACLE_MAXD];
+    for (int d = 0; d < D; ++d) w[d] = inv_mass ? inv_mass[d] : 1.0;
+    memcpy(qn, q + (size_t)c * D, sizeof(double) * D);
+    memcpy(pn, mom + (size_t)c * D, sizeof(double) * D);
+    memcpy(gn, grad + (size_t)c * D, sizeof(double) * D);
+    double lpn = lp ? lp[c] : 0.0;
+    for (int i = 0; i < L; ++i) {
+      if (friction) for (int d = 0; d < D; ++d) pn[d] = pn[d] * s_tab[i];  /* GRAHMC.py:197 */
+      for (int d = 0; d < D; ++d) pn[d] = pn[d] + half_eps * gn[d];        /* HMC.py:119 */
+      for (int d = 0; d < D; ++d) qn[d] = qn[d] + eps * (pn[d] * w[d]);    /* HMC.py:121 */
+      lpn = target_eval(&tg, qn, gn);                                      /* HMC.py:123 */
+      for (int d = 0; d < D; ++d) pn[d] = pn[d] + half_eps * gn[d];        /* HMC.py:127 */
+      if (friction) for (int d = 0; d < D; ++d) pn[d] = pn[d] * s_tab[i];  /* GRAHMC.py:209 */
+    }
+    if (q_out) memcpy(q_out + (size_t)c * D, qn, sizeof(double) * D);
+    if (mom_out) memcpy(mom_out + (size_t)c * D, pn, sizeof(double) * D);
+    if (grad_out) memcpy(grad_out + (size_t)c * D, gn, sizeof(double) * D);
+    if (lp_out) lp_out[c] = lpn;
+  }
+  free(s_tab);
+  return MCMC_OK;
+}
+
 static int check_common(const McmcParams* p, const McmcBuffers* b) {
   if (!p || !b || p->abi_version != MCMC_ABI_VERSION) return MCMC_EINVAL;
   if (p->n_dim < 1 || p->n_dim > ORACLE_MAXD || p->n_chains < 0 || p->num_samples < 0 || p->burn_in < 0)

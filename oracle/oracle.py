@@ -55,6 +55,7 @@ def lib() -> C.CDLL:
             getattr(L, n).argtypes = [C.POINTER(_abi.McmcParams), C.POINTER(_abi.McmcBuffers)]
         L.oracle_target_eval.argtypes = [C.POINTER(_abi.McmcParams), C.c_void_p, C.c_void_p, C.c_int64,
                                          C.c_void_p, C.c_void_p]
+        L.oracle_leapfrog.argtypes = [C.POINTER(_abi.McmcParams), C.c_int] + [C.c_void_p] * 10
         L.oracle_friction_table.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
                                             C.c_void_p, C.c_void_p]
         L.oracle_friction_table.restype = None
@@ -151,6 +152,22 @@ def target_eval(p: _abi.McmcParams, q, cov_inv=None, want_grad=True):
     ci = None if cov_inv is None else np.ascontiguousarray(cov_inv, dtype=np.float64)
     lib().oracle_target_eval(C.byref(p), _ptr(ci), _ptr(q), n, _ptr(lp), _ptr(g))
     return lp, g
+
+
+def leapfrog(p: _abi.McmcParams, q, mom, lp, grad, inv_mass=None, cov_inv=None, friction=False):
+    """(q, momentum, log_prob, grad) after p.num_steps steps: HMC.py:85-134 / GRAHMC.py:215-261 (friction=True)."""
+    q = np.ascontiguousarray(q, dtype=np.float64)
+    mom = np.ascontiguousarray(mom, dtype=np.float64)
+    grad = np.ascontiguousarray(grad, dtype=np.float64)
+    lp = None if lp is None else np.ascontiguousarray(lp, dtype=np.float64)
+    w = None if inv_mass is None else np.ascontiguousarray(inv_mass, dtype=np.float64)
+    ci = None if cov_inv is None else np.ascontiguousarray(cov_inv, dtype=np.float64)
+    qo, po, go, lo = np.empty_like(q), np.empty_like(mom), np.empty_like(grad), np.empty(q.shape[0])
+    rc = lib().oracle_leapfrog(C.byref(p), int(bool(friction)), _ptr(ci), _ptr(w), _ptr(q), _ptr(mom), _ptr(lp), _ptr(grad),
+                               _ptr(qo), _ptr(po), _ptr(lo), _ptr(go))
+    if rc != 0:
+        raise ValueError(f"oracle returned {rc}")
+    return qo, po, lo, go
 
 
 def friction_table(schedule_id, L, eps, gamma, steepness):
