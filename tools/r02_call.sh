@@ -50,6 +50,11 @@ multi)
   timeout 600 python -m pytest tests/test_multigpu_gpu.py tests/test_abi_gpu.py -m gpu -q --timeout 300 -p no:cacheprovider > $O/pytest_multi_$TAG.log 2>&1; echo "multi tests rc=$?"; tail -4 $O/pytest_multi_$TAG.log
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 > $O/bench_${TAG}_${N}gpu.json 2> $O/bench_${TAG}_${N}gpu.err; echo "bench rc=$?"; tail -c 2500 $O/bench_${TAG}_${N}gpu.json; grep -c "NCCL INFO" $O/bench_${TAG}_${N}gpu.err; grep -m3 "nranks\|NVLS\|Connected all" $O/bench_${TAG}_${N}gpu.err | cut -c1-200
   timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --impl reference --gpus $N --steps 2 --warmup 1 > $O/bench_ref_${TAG}_${N}gpu.json 2> /dev/null; echo "ref rc=$?"; tail -c 700 $O/bench_ref_${TAG}_${N}gpu.json ;;
+d2h)
+  N=$(nvidia-smi -L | wc -l)
+  { nvidia-smi topo -m 2>&1 | head -24; lscpu 2>/dev/null | grep -i "numa\|socket\|^CPU(s)\|model name"; echo "cgroup cpus: $(nproc)"
+    NCCL_DEBUG=WARN timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29514 tools/d2h_probe.py 2>&1 | grep "^{"
+  } > $O/d2h_probe_${TAG}_${N}gpu.txt 2>&1; echo "d2h rc=$?"; cat $O/d2h_probe_${TAG}_${N}gpu.txt ;;
 multicfg)
   N=$(nvidia-smi -L | wc -l)
   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 tools/run_configs.py --configs 3,5 --c4-chains 4194304 --out $O/configs_${TAG}_${N}gpu.jsonl > $O/configs_${TAG}_${N}gpu.log 2>&1; echo "configs rc=$?"; grep "^{" $O/configs_${TAG}_${N}gpu.log | cut -c1-400 ;;
