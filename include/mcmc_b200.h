@@ -275,6 +275,12 @@ int mcmc_sum_f64(const double* x, int64_t n, double* out, void* workspace, size_
    order, `perm` = the permutation that sorted them; out_z[perm[i]] = Phi^-1((r_i - 3/8)/(n + 1/4)) with
    r_i the average 1-based rank of sorted_vals[i] over ties.
 
+   mcmc_rank_normalize_fold: both rank-normalisations R-hat needs, from ONE sort done inside (ArviZ `_z_scale(ary)` for
+   the bulk and `_z_scale(abs(ary - median(ary)))` for the folded / tail R-hat).  x = the variable's n values in any
+   order (not modified); sorted_out = the values ascending (the caller takes the tail quantiles from it); z_bulk[i],
+   z_fold[i] = the z-scores of x[i].  Bit-identical to mcmc_rank_normalize applied to a sort of x and to a sort of the
+   folded values.  n < 2^31; workspace (256-byte aligned) of mcmc_rank_normalize_fold_workspace(n) bytes.
+
    mcmc_split_chain_stats: one variable laid out y[s*stride_s + c*stride_c].  Every chain c contributes
    two sequences of half_len draws: rows [0, half_len) and rows [second_half_row, second_half_row +
    half_len).  Outputs: acov_sum[t] = sum over the 2*n_chains sequences of the biased autocovariance at
@@ -282,6 +288,9 @@ int mcmc_sum_f64(const double* x, int64_t n, double* out, void* workspace, size_
    ESS follow from these on the host (Geyer truncation) after the sums have been all-reduced over the
    chain shards of a multi-GPU run.  Results are deterministic (fixed-order reductions). */
 int mcmc_rank_normalize(const double* sorted_vals, const int64_t* perm, int64_t n, double* out_z, void* stream);
+int mcmc_rank_normalize_fold_workspace(int64_t n, size_t* bytes);
+int mcmc_rank_normalize_fold(const double* x, int64_t n, double* sorted_out, double* z_bulk, double* z_fold, void* workspace,
+                             size_t workspace_bytes, void* stream);
 int mcmc_split_chain_stats_workspace(int64_t half_len, int64_t n_chains, int32_t n_lags, size_t* bytes);
 int mcmc_split_chain_stats(const double* y, int64_t half_len, int64_t second_half_row, int64_t n_chains,
                            int64_t stride_s, int64_t stride_c, int32_t n_lags, double* acov_sum,

@@ -82,7 +82,7 @@ EXPORTS = [
     "mcmc_hmc_run", "mcmc_grahmc_run", "mcmc_rwmh_run", "mcmc_nuts_run",
     "mcmc_run_host", "mcmc_host_arena_release", "mcmc_register_user_target", "mcmc_target_eval", "mcmc_leapfrog", "mcmc_philox_fill", "mcmc_friction_table",
     "mcmc_welford_finalize", "mcmc_welford_finalize_noalloc", "mcmc_chain_moments", "mcmc_da_init", "mcmc_da_update", "mcmc_da_reset", "mcmc_sum_f64", "mcmc_fp64_peak_probe",
-    "mcmc_rank_normalize", "mcmc_split_chain_stats_workspace", "mcmc_split_chain_stats",
+    "mcmc_rank_normalize", "mcmc_rank_normalize_fold_workspace", "mcmc_rank_normalize_fold", "mcmc_split_chain_stats_workspace", "mcmc_split_chain_stats",
 ]
 
 _LIBS: dict = {}
@@ -141,6 +141,8 @@ def lib(variant: str | None = None) -> C.CDLL:
     L.mcmc_sum_f64.argtypes = [_P, C.c_int64, _P, _P, C.c_size_t, _P]
     L.mcmc_fp64_peak_probe.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_float), _P]
     L.mcmc_rank_normalize.argtypes = [_P, _P, C.c_int64, _P, _P]
+    L.mcmc_rank_normalize_fold_workspace.argtypes = [C.c_int64, C.POINTER(C.c_size_t)]
+    L.mcmc_rank_normalize_fold.argtypes = [_P, C.c_int64, _P, _P, _P, _P, C.c_size_t, _P]
     L.mcmc_split_chain_stats_workspace.argtypes = [C.c_int64, C.c_int64, C.c_int32, C.POINTER(C.c_size_t)]
     L.mcmc_split_chain_stats.argtypes = [_P, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, _P, _P,
                                          _P, C.c_size_t, _P]

@@ -8,6 +8,9 @@
 //
 //   rank_normalize_kernel      z = Phi^-1((r - 3/8)/(N + 1/4)), r = average rank over ties, from the
 //                              sorted values + sorting permutation of one variable
+//   rank_normalize_fold_kernel the bulk z AND the z of the folded draws |x - median| from ONE sort: in the sorted array the
+//                              two sides of the median are already monotone in the distance, so a folded rank is the
+//                              element's position on its own side plus one binary search on the other side
 //   split_chain_stats_kernel   per (chain, half) sequence: mean and biased autocovariance at every lag
 //                              (direct O(n^2/2) products from a shared-memory tile, not an FFT:
 //                              43 GFLOP for 2.6M sequences of 128 draws), summed over the block's 32
@@ -15,6 +18,8 @@
 //   split_chain_final_kernel   fixed-order sum of the block partials -> sum_seq acov[t]; Chan merge of
 //                              the (count, mean, M2) of the sequence means  => deterministic results
 #include "common.cuh"
+
+#include <cub/device/device_radix_sort.cuh>
 
 namespace mcmc {
 
@@ -49,6 +54,150 @@ __global__ void __launch_bounds__(256) rank_normalize_kernel(const double* __res
   const double r = 0.5 * (double)(lo + hi) + 1.0;            // average of the 1-based ranks lo+1 .. hi+1
   const double p = (r - 0.375) / ((double)n + 0.25);
   out[perm[i]] = normcdfinv(p);
+}
+
+// ---- bulk and folded z-scores from one sort (ArviZ: _z_scale(split) and _z_scale(abs(split - median(split))))
+
+__global__ void iota_u32_kernel(uint32_t* __restrict__ p, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = (uint32_t)i;
+}
+
+// pivot[0] = median of the sorted values (np.median: mean of the two middle elements), pivot[1] = J = first index with
+// s[j] >= median (as a double; J < 2^32)
+__global__ void fold_pivot_kernel(const double* __restrict__ s, int64_t n, double* __restrict__ pivot) {
+  const double med = 0.5 * (s[(n - 1) / 2] + s[n / 2]);
+  int64_t a = 0, b = n;
+  while (a < b) {
+    const int64_t m = a + ((b - a) >> 1);
+    if (s[m] < med) a = m + 1; else b = m;
+  }
+  pivot[0] = med;
+  pivot[1] = (double)a;
+}
+
+__device__ __forceinline__ double rank_to_z(double less, double eq, double n) {
+  const double r = less + 0.5 * (eq + 1.0);                  // average of the 1-based ranks less+1 .. less+eq
+  return normcdfinv((r - 0.375) / (n + 0.25));
+}
+
+// Thread i owns the i-th smallest value.  d_j = |s[j] - med| is non-increasing for j < J and non-decreasing for j >= J
+// (a rounded subtraction is monotone, and s[j] - med is never 0 for s[j] != med), so among the folded values
+//   #(d < d_i) = (own side: distance in positions to J, past the run of equal d) + (other side: one binary search)
+// and the tie counts come from the same neighbours / searches.  All searches of a warp walk the same path (d_i is
+// monotone in i), so they stay in L1.  Ranks are exact half-integers: the z-scores equal those of a sort of the folded
+// values bit for bit.
+__global__ void __launch_bounds__(256) rank_normalize_fold_kernel(const double* __restrict__ s, const uint32_t* __restrict__ perm,
+                                                                  int64_t n, const double* __restrict__ pivot,
+                                                                  double* __restrict__ z_bulk, double* __restrict__ z_fold) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double x = s[i];
+  const double med = pivot[0];
+  const int64_t J = (int64_t)pivot[1];
+  const double dn = (double)n;
+  // ---- bulk: run [lo, hi] of values equal to x
+  int64_t lo = i, hi = i;
+  if (i > 0 && s[i - 1] == x) {
+    int64_t a = 0, b = i - 1;
+    while (a < b) {
+      const int64_t m = a + ((b - a) >> 1);
+      if (s[m] == x) b = m; else a = m + 1;
+    }
+    lo = a;
+  }
+  if (i + 1 < n && s[i + 1] == x) {
+    int64_t a = i + 1, b = n - 1;
+    while (a < b) {
+      const int64_t m = a + ((b - a + 1) >> 1);
+      if (s[m] == x) a = m; else b = m - 1;
+    }
+    hi = a;
+  }
+  const size_t dst = perm[i];
+  z_bulk[dst] = rank_to_z((double)lo, (double)(hi - lo + 1), dn);
+  // ---- folded
+#define FD(j) fabs(s[j] - med)
+  const double d = fabs(x - med);
+  int64_t less, eq;
+  if (i >= J) {
+    // own side [J, n): non-decreasing d.  Run [a, b] of equal d around i (wider than [lo, hi] only if distinct values
+    // round to the same distance)
+    int64_t a = lo > J ? lo : J, b = hi;
+    if (a > J && FD(a - 1) == d) {
+      int64_t u = J, v = a - 1;           // first index in [J, a-1] with d == d_i
+      while (u < v) {
+        const int64_t m = u + ((v - u) >> 1);
+        if (FD(m) == d) v = m; else u = m + 1;
+      }
+      a = u;
+    }
+    if (b + 1 < n && FD(b + 1) == d) {
+      int64_t u = b + 1, v = n - 1;       // last index in [b+1, n-1] with d == d_i
+      while (u < v) {
+        const int64_t m = u + ((v - u + 1) >> 1);
+        if (FD(m) == d) u = m; else v = m - 1;
+      }
+      b = u;
+    }
+    // other side [0, J): non-increasing d.  t = first index with d < d_i
+    int64_t u = 0, v = J;
+    while (u < v) {
+      const int64_t m = u + ((v - u) >> 1);
+      if (FD(m) < d) v = m; else u = m + 1;
+    }
+    const int64_t t = u;
+    int64_t t2 = t;                         // first index with d <= d_i
+    if (t > 0 && FD(t - 1) == d) {
+      int64_t p = 0, q = t - 1;
+      while (p < q) {
+        const int64_t m = p + ((q - p) >> 1);
+        if (FD(m) == d) q = m; else p = m + 1;
+      }
+      t2 = p;
+    }
+    less = (a - J) + (J - t);
+    eq = (b - a + 1) + (t - t2);
+  } else {
+    // own side [0, J): non-increasing d
+    int64_t a = lo, b = hi < J - 1 ? hi : J - 1;
+    if (a > 0 && FD(a - 1) == d) {
+      int64_t u = 0, v = a - 1;           // first index in [0, a-1] with d == d_i
+      while (u < v) {
+        const int64_t m = u + ((v - u) >> 1);
+        if (FD(m) == d) v = m; else u = m + 1;
+      }
+      a = u;
+    }
+    if (b + 1 < J && FD(b + 1) == d) {
+      int64_t u = b + 1, v = J - 1;       // last index in [b+1, J-1] with d == d_i
+      while (u < v) {
+        const int64_t m = u + ((v - u + 1) >> 1);
+        if (FD(m) == d) u = m; else v = m - 1;
+      }
+      b = u;
+    }
+    // other side [J, n): non-decreasing d.  t = first index with d >= d_i
+    int64_t u = J, v = n;
+    while (u < v) {
+      const int64_t m = u + ((v - u) >> 1);
+      if (FD(m) < d) u = m + 1; else v = m;
+    }
+    const int64_t t = u;
+    int64_t t2 = t;                         // one past the last index with d == d_i
+    if (t < n && FD(t) == d) {
+      int64_t p = t, q = n - 1;
+      while (p < q) {
+        const int64_t m = p + ((q - p + 1) >> 1);
+        if (FD(m) == d) p = m; else q = m - 1;
+      }
+      t2 = p + 1;
+    }
+    less = ((J - 1) - b) + (t - J);
+    eq = (b - a + 1) + (t2 - t);
+  }
+#undef FD
+  z_fold[dst] = rank_to_z((double)less, (double)eq, dn);
 }
 
 // y[s*stride_s + c*stride_c]; rows [0, n) are the first half, rows [row2, row2 + n) the second half.
@@ -200,6 +349,52 @@ int mcmc_rank_normalize(const double* sorted_vals, const int64_t* perm, int64_t 
   if (n == 0) return MCMC_OK;
   rank_normalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(sorted_vals, perm, n, out_z);
   return cuda_fail(cudaGetLastError(), "rank_normalize launch");
+}
+
+// workspace of mcmc_rank_normalize_fold: [pivot: 2 doubles][iota: n u32][perm: n u32][cub temp]
+static size_t rank_fold_ws(int64_t n, size_t* cub_bytes, size_t* off_iota, size_t* off_perm, size_t* off_cub) {
+  size_t tb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, (const double*)nullptr, (double*)nullptr, (const uint32_t*)nullptr,
+                                  (uint32_t*)nullptr, n, 0, 64, (cudaStream_t)0);
+  const size_t idx = (((size_t)n * sizeof(uint32_t)) + 255) & ~(size_t)255;
+  if (cub_bytes) *cub_bytes = tb;
+  if (off_iota) *off_iota = 256;
+  if (off_perm) *off_perm = 256 + idx;
+  if (off_cub) *off_cub = 256 + 2 * idx;
+  return 256 + 2 * idx + tb + 256;
+}
+
+int mcmc_rank_normalize_fold_workspace(int64_t n, size_t* bytes) {
+  if (!bytes || n < 0 || n >= ((int64_t)1 << 31)) { set_error("rank_normalize_fold: n outside [0, 2^31)"); return n >= ((int64_t)1 << 31) ? MCMC_ENOTSUP : MCMC_EINVAL; }
+  *bytes = rank_fold_ws(n > 0 ? n : 1, nullptr, nullptr, nullptr, nullptr);
+  return MCMC_OK;
+}
+
+int mcmc_rank_normalize_fold(const double* x, int64_t n, double* sorted_out, double* z_bulk, double* z_fold, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+  if ((!x || !sorted_out || !z_bulk || !z_fold) && n > 0) { set_error("null argument"); return MCMC_EINVAL; }
+  if (n < 0) { set_error("negative size"); return MCMC_EINVAL; }
+  if (n >= ((int64_t)1 << 31)) { set_error("rank_normalize_fold: more than 2^31 - 1 values (use mcmc_rank_normalize)"); return MCMC_ENOTSUP; }
+  int nd = 0;
+  if (cudaGetDeviceCount(&nd) != cudaSuccess || nd == 0) { cudaGetLastError(); set_error("no CUDA device (there is no CPU fallback)"); return MCMC_ECUDA; }
+  if (n == 0) return MCMC_OK;
+  size_t tb = 0, o_iota = 0, o_perm = 0, o_cub = 0;
+  const size_t need = rank_fold_ws(n, &tb, &o_iota, &o_perm, &o_cub);
+  if (!workspace || workspace_bytes < need) { set_error("rank_normalize_fold needs %zu workspace bytes", need); return MCMC_EWORKSPACE; }
+  if (((uintptr_t)workspace) & 255) { set_error("rank_normalize_fold: workspace must be 256-byte aligned"); return MCMC_EINVAL; }
+  char* w = (char*)workspace;
+  double* pivot = (double*)w;
+  uint32_t* iota = (uint32_t*)(w + o_iota);
+  uint32_t* perm = (uint32_t*)(w + o_perm);
+  cudaStream_t s = (cudaStream_t)stream;
+  const unsigned grid = (unsigned)((n + 255) / 256);
+  iota_u32_kernel<<<grid, 256, 0, s>>>(iota, n);
+  if (int rc = cuda_fail(cub::DeviceRadixSort::SortPairs((void*)(w + o_cub), tb, x, sorted_out, (const uint32_t*)iota, perm, n, 0, 64, s),
+                         "cub::DeviceRadixSort::SortPairs"))
+    return rc;
+  fold_pivot_kernel<<<1, 1, 0, s>>>(sorted_out, n, pivot);
+  rank_normalize_fold_kernel<<<grid, 256, 0, s>>>(sorted_out, perm, n, pivot, z_bulk, z_fold);
+  return cuda_fail(cudaGetLastError(), "rank_normalize_fold launch");
 }
 
 int mcmc_split_chain_stats_workspace(int64_t half_len, int64_t n_chains, int32_t n_lags, size_t* bytes) {

@@ -60,6 +60,27 @@ def rank_normalize(x: torch.Tensor) -> torch.Tensor:
     return out.reshape(x.shape), vals
 
 
+def rank_normalize_fold(x: torch.Tensor):
+    """ArviZ `_z_scale(x)` and `_z_scale(abs(x - median(x)))` over ALL elements of x from one sort
+    (mcmc_rank_normalize_fold).  Returns (z_bulk, z_fold, sorted values); bit-identical to two rank_normalize calls."""
+    _require_cuda(x)
+    L = _abi.lib()
+    flat = x.reshape(-1).contiguous()
+    n = flat.numel()
+    if n >= 2 ** 31:
+        z, vals = rank_normalize(x)
+        med = 0.5 * (vals[(n - 1) // 2] + vals[n // 2])
+        return z, rank_normalize((x - med).abs())[0], vals
+    nb = C.c_size_t(0)
+    _abi.check(L.mcmc_rank_normalize_fold_workspace(n, C.byref(nb)))
+    ws = torch.empty((nb.value,), dtype=torch.uint8, device=x.device)
+    vals, zb, zf = torch.empty_like(flat), torch.empty_like(flat), torch.empty_like(flat)
+    _abi.check(L.mcmc_set_device(x.device.index))
+    _abi.check(L.mcmc_rank_normalize_fold(_ptr(flat), n, _ptr(vals), _ptr(zb), _ptr(zf), _ptr(ws), nb.value, _stream(x.device)))
+    ws.record_stream(torch.cuda.current_stream(x.device))
+    return zb.reshape(x.shape), zf.reshape(x.shape), vals
+
+
 def split_chain_stats(y: torch.Tensor, half_len: int, second_half_row: int, n_lags: Optional[int] = None):
     """y: (rows, C) float64 CUDA tensor (any strides).  Returns (acov_sum (n_lags,), mean_stats (3,)) on the device."""
     _require_cuda(y)
@@ -149,13 +170,10 @@ def _variable_device(col: torch.Tensor, max_lag: Optional[int] = None):
     if S < 4:
         raise ValueError("need at least 4 draws per chain")
     split, n = _split_rows(col.to(torch.float64))
-    # bulk: rank-normalised split chains
-    z, sorted_vals = rank_normalize(split)
+    # bulk: rank-normalised split chains; tail R-hat: folded around the median of the split draws — one sort for both
+    z, zf, sorted_vals = rank_normalize_fold(split)
     a_bulk, s_bulk = split_chain_stats(z, n, n, max_lag)
-    # tail R-hat: folded around the median of the split draws
     N = sorted_vals.numel()
-    med = 0.5 * (sorted_vals[(N - 1) // 2] + sorted_vals[N // 2])
-    zf, _ = rank_normalize((split - med).abs())
     a_fold, s_fold = split_chain_stats(zf, n, n, 1)
     # tail ESS: indicators of the 5% / 95% quantiles of ALL draws
     if S == 2 * n:

@@ -45,6 +45,67 @@ def test_rank_normalize_constant_and_stuck_columns(gpu_lib):
     np.testing.assert_allclose(z.cpu().numpy(), O.z_scale(x), rtol=0, atol=2e-13)
 
 
+def _fold_cases():
+    rng = np.random.default_rng(5)
+    yield "normal_100003", rng.standard_normal(100003)
+    for n in (1, 2, 3, 4, 5, 6):
+        yield f"tiny_{n}", rng.standard_normal(n)
+    yield "heavy_ties_digits", rng.integers(0, 10, 50000).astype(np.float64)          # ties on both sides and across the fold
+    yield "rounded_normal_2d", np.round(rng.standard_normal((64, 37)), 1)
+    yield "constant", np.full(4097, 3.25)
+    yield "symmetric_exact", np.concatenate([np.arange(-300, 301) / 8.0, np.arange(-300, 301) / 8.0])   # every distance twice per side
+    yield "median_repeated", np.concatenate([rng.standard_normal(999), np.zeros(500), -rng.random(300), rng.random(300)])
+    yield "signed_zeros", np.array([0.0, -0.0, 1.0, -1.0, 0.0, -0.0, 2.0, -2.0, -0.0])
+    yield "two_values", np.array([1.0] * 700 + [2.0] * 301)
+    yield "one_sided", np.concatenate([np.zeros(600), rng.random(400)])                   # median = minimum: empty left side
+    yield "wide_range", rng.standard_normal(20001) * 10.0 ** rng.integers(-8, 8, 20001)
+    yield "stuck_chains", _mcmc_like(rng, 128, 64, 1, p_stay=0.6)[:, :, 0]
+
+
+@pytest.mark.parametrize("name", [n for n, _ in _fold_cases()])
+def test_rank_normalize_fold_is_bit_identical_to_two_sorts(gpu_lib, name):
+    """mcmc_rank_normalize_fold (one sort; the folded ranks from the two monotone sides of the median) against the
+    straightforward path — sort, rank, fold around the median, sort again, rank — and against the NumPy restatement of
+    ArviZ.  Ranks are exact half-integers, so the z-scores must agree bit for bit."""
+    from mcmc_b200 import diagnostics as DG
+    x = dict(_fold_cases())[name]
+    xt = torch.from_numpy(np.ascontiguousarray(x)).cuda()
+    zb, zf, vals = DG.rank_normalize_fold(xt)
+    z0, v0 = DG.rank_normalize(xt)
+    n = v0.numel()
+    med = 0.5 * (v0[(n - 1) // 2] + v0[n // 2])
+    zf0, _ = DG.rank_normalize((xt - med).abs())
+    assert torch.equal(vals, v0)
+    assert torch.equal(zb, z0), name
+    assert torch.equal(zf, zf0), name
+    assert zb.shape == xt.shape and zf.shape == xt.shape
+    if x.size >= 4:
+        xa = np.asarray(x, dtype=np.float64)
+        np.testing.assert_allclose(zf.cpu().numpy(), O.z_scale(np.abs(xa - np.median(xa))), rtol=0, atol=2e-13)
+
+
+def test_rank_normalize_fold_large_and_errors(gpu_lib):
+    import ctypes as C
+    from mcmc_b200 import _abi, diagnostics as DG
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.randn((1 << 22) + 7, dtype=torch.float64, device="cuda", generator=g)
+    m = x.numel() // 5
+    x[0:5 * m:5] = x[1:5 * m:5]                                                           # 20% exact duplicates
+    zb, zf, vals = DG.rank_normalize_fold(x)
+    z0, v0 = DG.rank_normalize(x)
+    med = 0.5 * (v0[(x.numel() - 1) // 2] + v0[x.numel() // 2])
+    assert torch.equal(zb, z0) and torch.equal(zf, DG.rank_normalize((x - med).abs())[0]) and torch.equal(vals, v0)
+    L = _abi.lib("fast")
+    nb = C.c_size_t(0)
+    assert L.mcmc_rank_normalize_fold_workspace(1 << 31, C.byref(nb)) == _abi.ENOTSUP
+    assert L.mcmc_rank_normalize_fold_workspace(1000, C.byref(nb)) == 0 and nb.value > 8000
+    p = lambda t: C.c_void_p(t.data_ptr())
+    small = torch.empty(16, dtype=torch.uint8, device="cuda")
+    assert L.mcmc_rank_normalize_fold(p(x), 1000, p(vals), p(zb), p(zf), p(small), 16, None) == _abi.EWORKSPACE
+    assert L.mcmc_rank_normalize_fold(None, 1000, p(vals), p(zb), p(zf), p(small), 16, None) == _abi.EINVAL
+    assert L.mcmc_rank_normalize_fold(None, 0, None, None, None, None, 0, None) == 0
+
+
 @pytest.mark.parametrize("n,C", [(50, 7), (128, 100), (257, 33), (900, 40)])
 def test_split_chain_stats_vs_numpy(gpu_lib, n, C):
     """n=900 exceeds the shared-memory tile and takes the global-scratch variant of the kernel."""

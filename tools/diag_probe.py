@@ -42,6 +42,8 @@ if __name__ == "__main__":
     print(f"  torch.sort {flat.numel()/1e6:.1f} M doubles: {ms:.2f} ms")
     ms, (z, _) = t(lambda: DG.rank_normalize(split))
     print(f"  rank_normalize (sort + kernel): {ms:.2f} ms")
+    ms, _ = t(lambda: DG.rank_normalize_fold(split))
+    print(f"  rank_normalize_fold (one pair sort with u32 indices + fused bulk/fold rank kernel): {ms:.2f} ms")
     ms, _ = t(lambda: DG.split_chain_stats(z, n, n, None))
     print(f"  split_chain_stats all lags: {ms:.2f} ms")
     ms, _ = t(lambda: DG.split_chain_stats(z, n, n, 1))
