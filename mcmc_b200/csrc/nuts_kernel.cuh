@@ -93,16 +93,18 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
   extern __shared__ __align__(16) double smem[];
   double* sm_w = smem;
   double* sm_sqw = smem + n;
-  double* sm_tab = smem + 2 * n;
+  double* sm_epsw = smem + 2 * n;   // eps * w[d]: the drift of the fast build is one DFMA per dimension
+  double* sm_tab = smem + 3 * n;
   // lane tile: slot(s, d) = wbase[(s*n + d)*32] — conflict-free in shared memory, one coalesced 256-byte request in L2
   double* wbase;
-  if (kSmemSlots) wbase = smem + ((2 * n + target_table_len(TID, n) + 1) / 2) * 2 + tid;
+  if (kSmemSlots) wbase = smem + ((3 * n + target_table_len(TID, n) + 1) / 2) * 2 + tid;
   else wbase = a.slots + (size_t)blockIdx.x * ((size_t)SL_COUNT * n * 32) + tid;
 #define SLOT(s, d) wbase[((s) * n + (d)) * 32]
 
   for (int d = tid; d < n; d += BLOCK) {
     const double w = a.b.inv_mass ? a.b.inv_mass[d] : 1.0;
     sm_w[d] = w;
+    sm_epsw[d] = eps * w;
 #if MCMC_IS_FAITHFUL
     sm_sqw[d] = sqrt(w);        // p0 = z / sqrt(w), NUTS.py:219
 #else
@@ -119,6 +121,11 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
 
   // Working point = the tree end that was integrated last (direction reg_dir).  It stays in registers; the
   // opposite end is always current in the O slots and the two are swapped when the tree turns round.
+  // The working momentum is held SIGN-FOLDED: ps = reg_dir * p.  Integrating backwards (step -eps, NUTS.py:155) is
+  // integrating -p forwards, and negation commutes with every rounding, so the step below is direction-free — the
+  // same kick and drift constants for every lane, bit-identical values — and only the bookkeeping (turn-round, U-turn
+  // test) converts.  A lone warp is bound by the issue rate of the fp64 pipe (one warp-instruction per two cycles), so
+  // what a step costs is its fp64 instruction count: the fast build's drift is fma(ps, eps*w, qs), one instead of two.
   double qs[N], ps[N], gs[N];
   double lps = 0.0;
   double lpp = 0.0;
@@ -126,7 +133,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
 
   // per-transition scalars
   double h0 = 0.0, log_u = 0.0, sum_alpha = 0.0, sa = 0.0, h_new = 0.0, u_prop = 0.0;
-  double se = 0.0, hse = 0.0;
+  const double heps = 0.5 * eps;   // NUTS.py:107 with the direction folded into ps
   int n_valid = 1, n_steps = 0, depth = 0, direction = 1, reg_dir = 1, k = 0, num_steps = 0;
   bool diverged = false, in_subtree = false, in_transition = false;
   // per-item state
@@ -231,8 +238,10 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
           eop[d % kSumWays] += e * SLOT(SL_PO, d);
           ewp[d % kSumWays] += e * ps[d];
         }
+        // ps = reg_dir * p_work, so ew = reg_dir * (e . p_work):  right end (e.p_other, e.p_work) = (eo, ew);
+        // left end (-(e.p_work), -(e.p_other)) = (ew, -eo)
         const double eo = sum_ways(eop), ew = sum_ways(ewp);
-        const double dl = reg_dir > 0 ? eo : -ew, dr = reg_dir > 0 ? ew : -eo;
+        const double dl = reg_dir > 0 ? eo : ew, dr = reg_dir > 0 ? ew : -eo;
         u_turn = (dl < 0) | (dr < 0);
       }
       if (!in_transition) {
@@ -279,29 +288,31 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
         }
         direction = (u_dir < 0.5) ? 1 : -1;  // bernoulli(0.5) = uniform < 0.5
         if (reg_dir == 0) {
-          // first subtree of the transition: the initial state is also the end opposite to `direction`
+          // first subtree of the transition: the initial state (true momentum in ps) is also the end opposite to
+          // `direction`; the working copy becomes direction * p
 #pragma unroll
           for (int d = 0; d < n; ++d) {
             SLOT(SL_QO, d) = qs[d];
             SLOT(SL_PO, d) = ps[d];
             SLOT(SL_GO, d) = gs[d];
+            if (direction < 0) ps[d] = -ps[d];
           }
         } else if (direction != reg_dir) {
-          // the tree turns round: the working end and the opposite end change places
+          // the tree turns round: the working end and the opposite end change places.  The slots hold TRUE momenta:
+          // reg_dir * ps goes out, direction * (slot) comes in — with direction == -reg_dir both are "negate iff
+          // the new direction is +1 / -1"
 #pragma unroll
           for (int d = 0; d < n; ++d) {
             const double tq = SLOT(SL_QO, d), tp = SLOT(SL_PO, d), tg = SLOT(SL_GO, d);
             SLOT(SL_QO, d) = qs[d];
-            SLOT(SL_PO, d) = ps[d];
+            SLOT(SL_PO, d) = reg_dir < 0 ? -ps[d] : ps[d];
             SLOT(SL_GO, d) = gs[d];
-            qs[d] = tq; ps[d] = tp; gs[d] = tg;
+            qs[d] = tq; ps[d] = direction < 0 ? -tp : tp; gs[d] = tg;
           }
         }
         reg_dir = direction;
         num_steps = 1 << depth;
         k = num_steps;
-        se = direction * eps;  // NUTS.py:155
-        hse = 0.5 * se;        // NUTS.py:107
         sa = 0.0;
         lps = NAN;
         in_subtree = true;
@@ -386,14 +397,18 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
     if (k > 0) {
 #pragma unroll
       for (int d = 0; d < n; ++d) {
-        ps[d] = ps[d] + hse * gs[d];              // NUTS.py:107
-        qs[d] = qs[d] + se * (ps[d] * sm_w[d]);   // NUTS.py:109
+        ps[d] = ps[d] + heps * gs[d];             // NUTS.py:107 (ps = direction * p, see above)
+#if MCMC_IS_FAITHFUL
+        qs[d] = qs[d] + eps * (ps[d] * sm_w[d]);  // NUTS.py:109
+#else
+        qs[d] = fma(ps[d], sm_epsw[d], qs[d]);
+#endif
       }
       lps = target_eval<TID, DS, true, true>(a.t, n, qs, gs, sm_tab);  // NUTS.py:111
       double kinp[kSumWays] = {0.0};
 #pragma unroll
       for (int d = 0; d < n; ++d) {
-        ps[d] = ps[d] + hse * gs[d];              // NUTS.py:115
+        ps[d] = ps[d] + heps * gs[d];             // NUTS.py:115
         kinp[d % kSumWays] += (ps[d] * ps[d]) * sm_w[d];
       }
       h_new = -lps + 0.5 * sum_ways(kinp);        // NUTS.py:178 / :282
@@ -430,7 +445,7 @@ int launch_nuts_variant(const Launch& l) {
   const int n = l.p.n_dim;
   const int tabn = target_table_len(TID, n);
   const size_t tile = (size_t)SL_COUNT * n * 32;   // doubles per warp
-  const size_t smem = ((size_t)((2 * n + tabn + 1) / 2) * 2 + (DS > 0 ? tile : 0)) * sizeof(double);
+  const size_t smem = ((size_t)((3 * n + tabn + 1) / 2) * 2 + (DS > 0 ? tile : 0)) * sizeof(double);
   const NutsWs ws = nuts_ws_layout(l.p);
   if (!l.b.workspace || l.b.workspace_bytes < ws.total) {
     set_error("nuts: workspace of %zu bytes required (got %zu)", ws.total, l.b.workspace_bytes);
