@@ -170,9 +170,17 @@ __device__ __forceinline__ double target_eval(const TargetCtx& t, const int n_rt
       for (int d = 1; d < n; ++d) g[d] = q[d] * niv;
     }
 #endif
-    if (WANT_G) g[0] = -x0 / 9.0 + 0.5 * sv - 0.5 * t.c[2];
+#if MCMC_IS_FAITHFUL
+    const double x0v = x0 / 9.0;                 // targets.py:172-175: x[0] / 3**2
+    const double x0x0v = x0 * x0 / 9.0;
+#else
+    // the two divisions by the constant variance were 16 dependent DFMAs per evaluation (reciprocal iteration + correction)
+    const double x0v = x0 * (1.0 / 9.0);
+    const double x0x0v = x0 * x0v;
+#endif
+    if (WANT_G) g[0] = -x0v + 0.5 * sv - 0.5 * t.c[2];
     if (WANT_LP) {
-      const double lp0 = -0.5 * (x0 * x0 / 9.0 + t.c[0]);
+      const double lp0 = -0.5 * (x0x0v + t.c[0]);
       const double lpr = -0.5 * (sv + t.c[2] * x0 + t.c[1]);
       lp = lp0 + lpr;
     }
