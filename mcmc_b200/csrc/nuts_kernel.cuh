@@ -133,6 +133,11 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
 
   // per-transition scalars
   double h0 = 0.0, log_u = 0.0, sum_alpha = 0.0, sa = 0.0, h_new = 0.0, u_prop = 0.0;
+  // The Metropolis weight exp(min(0, h0 - h)) of a step (NUTS.py:179-181) is only ever summed.  Its argument is parked in
+  // `pend` and exponentiated at the START of the lane's next step, where the ~25-deep dependent chain hides under the
+  // kicks and drifts instead of ending the step (a lone lane waited ~15% of its time there); the subtree-end bookkeeping
+  // adds the last one.  Same additions in the same order (exp(-inf) = +0 where nothing is parked): bit-identical.
+  double pend = -INFINITY;
   const double heps = 0.5 * eps;   // NUTS.py:107 with the direction folded into ps
   int n_valid = 1, n_steps = 0, depth = 0, direction = 1, reg_dir = 1, k = 0, num_steps = 0;
   bool diverged = false, in_subtree = false, in_transition = false;
@@ -208,6 +213,8 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
         const bool is_div = (h_new - h0) > delta_max;
         const bool is_valid = in_slice && !is_div;
         const int n_valid_new = is_valid ? num_steps : 0;
+        sa = sa + exp_nonpos(pend);   // the weight of the subtree's last step
+        pend = -INFINITY;
         const int total_valid = n_valid + n_valid_new;
         float accept_prob = 0.0f;  // float32, NUTS.py:331-335
         if (total_valid > 0 && is_valid)
@@ -395,6 +402,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
 
     // ------------------------------------------------------------ one leapfrog step (convergent, hot)
     if (k > 0) {
+      sa = sa + exp_nonpos(pend);                 // the previous step's weight (NUTS.py:179-181), see `pend`
 #pragma unroll
       for (int d = 0; d < n; ++d) {
         ps[d] = ps[d] + heps * gs[d];             // NUTS.py:107 (ps = direction * p, see above)
@@ -412,7 +420,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
         kinp[d % kSumWays] += (ps[d] * ps[d]) * sm_w[d];
       }
       h_new = -lps + 0.5 * sum_ways(kinp);        // NUTS.py:178 / :282
-      sa = sa + exp_nonpos(min_nan(0.0, h0 - h_new));    // NUTS.py:179-181
+      pend = min_nan(0.0, h0 - h_new);
       k -= 1;
     } else if (__activemask() == 0xffffffffu) {
       __nanosleep(100);  // every lane of the warp is waiting for another warp's item (or finished)
