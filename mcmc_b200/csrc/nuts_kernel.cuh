@@ -74,6 +74,15 @@ constexpr int kNutsMinBlocks = MCMC_NUTS_MINBLOCKS;
 #define MCMC_NUTS_BK_LANES 16
 #endif
 constexpr int kNutsBkTrips = MCMC_NUTS_BK_TRIPS, kNutsBkLanes = MCMC_NUTS_BK_LANES;
+// Steps per loop trip.  The loop control of a trip (three votes, the convergence barrier of __all_sync, ~30 kernel-parameter
+// reloads) costs a lone lane ~250 cycles — a quarter of its step time (profiles/nuts_experiments_r02.txt section 7).  So a
+// trip runs r = min(steps left over all stepping lanes, kNutsInner) steps: every stepping lane has at least r to do, so
+// they stay in lockstep and nobody idles inside; lanes waiting for bookkeeping wait r steps instead of one (they already
+// wait up to kNutsBkTrips).  Purely a schedule: results are unchanged.
+#ifndef MCMC_NUTS_INNER
+#define MCMC_NUTS_INNER 8
+#endif
+constexpr int kNutsInner = MCMC_NUTS_INNER;
 
 template <int TID, int DS, int BLOCK>
 __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kernel(const NutsKArgs a) {
@@ -400,8 +409,16 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
       }
     }
 
-    // ------------------------------------------------------------ one leapfrog step (convergent, hot)
+    // ------------------------------------------------------------ leapfrog steps (convergent, hot)
+    int n_inner = 1;
+    if (kNutsInner > 1) {
+      n_inner = __reduce_min_sync(0xffffffffu, k > 0 ? k : 0x7fffffff);
+      n_inner = n_inner < kNutsInner ? n_inner : kNutsInner;
+      since_bk += n_inner - 1;
+    }
     if (k > 0) {
+#pragma unroll 1
+     for (int inner = 0; inner < n_inner; ++inner) {
       sa = sa + exp_nonpos(pend);                 // the previous step's weight (NUTS.py:179-181), see `pend`
 #pragma unroll
       for (int d = 0; d < n; ++d) {
@@ -422,6 +439,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
       h_new = -lps + 0.5 * sum_ways(kinp);        // NUTS.py:178 / :282
       pend = min_nan(0.0, h0 - h_new);
       k -= 1;
+     }
     } else if (__activemask() == 0xffffffffu) {
       __nanosleep(100);  // every lane of the warp is waiting for another warp's item (or finished)
     }
