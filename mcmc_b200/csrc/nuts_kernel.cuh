@@ -132,8 +132,9 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
   // opposite end is always current in the O slots and the two are swapped when the tree turns round.
   // The working momentum is held SIGN-FOLDED: ps = reg_dir * p.  Integrating backwards (step -eps, NUTS.py:155) is
   // integrating -p forwards, and negation commutes with every rounding, so the step below is direction-free — the
-  // same kick and drift constants for every lane, bit-identical values — and only the bookkeeping (turn-round, U-turn
-  // test) converts.  A lone warp is bound by the issue rate of the fp64 pipe (one warp-instruction per two cycles), so
+  // same kick and drift constants for every lane, bit-identical values.  The opposite end's momentum in the PO slot is
+  // folded the same way with ITS outward direction (-reg_dir), so a turn-round is a plain exchange and the U-turn test
+  // reads both dot products with a fixed sign.  A lone warp is bound by the issue rate of the fp64 pipe (one warp-instruction per two cycles), so
   // what a step costs is its fp64 instruction count: the fast build's drift is fma(ps, eps*w, qs), one instead of two.
   double qs[N], ps[N], gs[N];
   double lps = 0.0;
@@ -254,11 +255,11 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
           eop[d % kSumWays] += e * SLOT(SL_PO, d);
           ewp[d % kSumWays] += e * ps[d];
         }
-        // ps = reg_dir * p_work, so ew = reg_dir * (e . p_work):  right end (e.p_other, e.p_work) = (eo, ew);
-        // left end (-(e.p_work), -(e.p_other)) = (ew, -eo)
+        // Both momenta are folded with their end's OUTWARD direction: ps = reg_dir * p_work, PO slot = -reg_dir * p_other.
+        // So e.p_work = reg_dir * ew and e.p_other = -reg_dir * eo, and in either orientation the pair (dl, dr) is
+        // {-eo, ew}: right end (e.p_other, e.p_work) = (-eo, ew); left end (-(e.p_work), -(e.p_other)) = (ew, -eo)
         const double eo = sum_ways(eop), ew = sum_ways(ewp);
-        const double dl = reg_dir > 0 ? eo : ew, dr = reg_dir > 0 ? ew : -eo;
-        u_turn = (dl < 0) | (dr < 0);
+        u_turn = (-eo < 0) | (ew < 0);
       }
       if (!in_transition) {
         // new transition: momentum, energy, slice (NUTS.py:217-241).  Both tree ends are the current state
@@ -304,26 +305,26 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
         }
         direction = (u_dir < 0.5) ? 1 : -1;  // bernoulli(0.5) = uniform < 0.5
         if (reg_dir == 0) {
-          // first subtree of the transition: the initial state (true momentum in ps) is also the end opposite to
-          // `direction`; the working copy becomes direction * p
+          // first subtree of the transition: the initial state (true momentum p0 in ps) is both ends.  Each end keeps
+          // its momentum folded with its own outward direction: working copy direction * p0, other end -direction * p0
 #pragma unroll
           for (int d = 0; d < n; ++d) {
+            const double pw = direction < 0 ? -ps[d] : ps[d];
             SLOT(SL_QO, d) = qs[d];
-            SLOT(SL_PO, d) = ps[d];
+            SLOT(SL_PO, d) = -pw;
             SLOT(SL_GO, d) = gs[d];
-            if (direction < 0) ps[d] = -ps[d];
+            ps[d] = pw;
           }
         } else if (direction != reg_dir) {
-          // the tree turns round: the working end and the opposite end change places.  The slots hold TRUE momenta:
-          // reg_dir * ps goes out, direction * (slot) comes in — with direction == -reg_dir both are "negate iff
-          // the new direction is +1 / -1"
+          // the tree turns round: the working end and the opposite end change places — a plain exchange, because each
+          // momentum is already folded with the direction its end is integrated in
 #pragma unroll
           for (int d = 0; d < n; ++d) {
             const double tq = SLOT(SL_QO, d), tp = SLOT(SL_PO, d), tg = SLOT(SL_GO, d);
             SLOT(SL_QO, d) = qs[d];
-            SLOT(SL_PO, d) = reg_dir < 0 ? -ps[d] : ps[d];
+            SLOT(SL_PO, d) = ps[d];
             SLOT(SL_GO, d) = gs[d];
-            qs[d] = tq; ps[d] = direction < 0 ? -tp : tp; gs[d] = tg;
+            qs[d] = tq; ps[d] = tp; gs[d] = tg;
           }
         }
         reg_dir = direction;
