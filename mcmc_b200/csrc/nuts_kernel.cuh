@@ -149,14 +149,15 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
   // adds the last one.  Same additions in the same order (exp(-inf) = +0 where nothing is parked): bit-identical.
   double pend = -INFINITY;
   const double heps = 0.5 * eps;   // NUTS.py:107 with the direction folded into ps
-  int n_valid = 1, n_steps = 0, depth = 0, direction = 1, reg_dir = 1, k = 0, num_steps = 0;
+  // (steps of the subtree under way = 1 << depth and steps so far = (1 << depth) - 1 are recomputed where needed: every
+  // register this loop does not hold is one ptxas can schedule the step with)
+  int n_valid = 1, depth = 0, direction = 1, reg_dir = 1, k = 0;
   bool diverged = false, in_subtree = false, in_transition = false;
   // per-item state
   bool done = false, have_item = false, waiting = false;
   int64_t it = 0, it_item_end = 0, chain = 0;
   unsigned int chunk = 0;
-  double wcount = 0.0;
-  unsigned long long n_grad = 0, sum_depth = 0, n_div = 0, acc_total = 0;
+  unsigned int n_grad = 0, sum_depth = 0, n_div = 0, acc_total = 0;   // per-lane tallies, flushed before they can wrap
   const unsigned int n_items = (unsigned int)C * (unsigned int)a.n_chunks;
 
   int since_bk = 0;
@@ -211,7 +212,6 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
           lpp = __ldcg(a.home_lp + chain);
           acc = __ldcg(a.home_acc + chain);
         }
-        wcount = a.b.welford_count + (double)(it > B ? it - B : 0);
         have_item = true;
         in_transition = false;
         in_subtree = false;
@@ -222,6 +222,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
         const bool in_slice = log_u <= -h_new;
         const bool is_div = (h_new - h0) > delta_max;
         const bool is_valid = in_slice && !is_div;
+        const int num_steps = 1 << depth;   // the subtree that just ended
         const int n_valid_new = is_valid ? num_steps : 0;
         sa = sa + exp_nonpos(pend);   // the weight of the subtree's last step
         pend = -INFINITY;
@@ -239,8 +240,15 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
         }
         n_valid = total_valid;
         sum_alpha = sum_alpha + sa;
-        n_steps += num_steps;
-        n_grad += (unsigned long long)num_steps;
+        n_grad += (unsigned int)num_steps;
+        if (n_grad > 0x7f000000u || acc_total > 0x7f000000u || sum_depth > 0x7f000000u) {
+          if (a.b.counters) {
+            atomicAdd(a.b.counters + 0, (unsigned long long)acc_total);
+            atomicAdd(a.b.counters + 1, (unsigned long long)n_grad);
+            atomicAdd(a.b.counters + 2, (unsigned long long)sum_depth);
+          }
+          acc_total = 0; n_grad = 0; sum_depth = 0;
+        }
         depth += 1;
         diverged = diverged || is_div;
         in_subtree = false;
@@ -288,7 +296,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
         h0 = -lpp + 0.5 * sum_ways(kinp);
         const double lgu = a.logu ? a.logu[(size_t)(it - a.z_it0) * C + chain] : log(a.b.u_inject[(size_t)it * C + chain]);
         log_u = lgu - h0;
-        n_valid = 1; n_steps = 0; sum_alpha = 0.0; depth = 0; diverged = false;
+        n_valid = 1; sum_alpha = 0.0; depth = 0; diverged = false;
         in_transition = true;
         reg_dir = 0;   // registers hold BOTH ends
         u_turn = false;
@@ -328,18 +336,18 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
           }
         }
         reg_dir = direction;
-        num_steps = 1 << depth;
-        k = num_steps;
+        k = 1 << depth;
         sa = 0.0;
         lps = NAN;
         in_subtree = true;
       } else {
         // transition finished (NUTS.py:384-396): the proposal becomes the state
+        const int n_steps = (1 << depth) - 1;   // 1 + 2 + ... over the `depth` subtrees of this transition
         double map = sum_alpha / (double)(n_steps > 1 ? n_steps : 1);
         if (isnan(map) || isinf(map)) map = 0.65;
         acc += 1;
-        sum_depth += (unsigned long long)depth;
-        n_div += diverged ? 1ull : 0ull;
+        sum_depth += (unsigned int)depth;
+        n_div += diverged ? 1u : 0u;
         const int64_t si = it - B;
         if (si >= 0) {
           const size_t o = (size_t)si * C + chain;
@@ -354,7 +362,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
           if (a.b.tree_depths) a.b.tree_depths[o] = depth;
           if (a.b.mean_accept_probs) a.b.mean_accept_probs[o] = map;
           if (do_w) {  // tuning/welford.py:42-59; L2 accesses: the previous item of the chain may have run on another SM
-            wcount += 1.0;
+            const double wcount = a.b.welford_count + (double)(it - B + 1);   // samples folded so far, this one included
             double* wm = a.b.welford_mean + chain * n;
             double* w2 = a.b.welford_m2 + chain * n;
 #if !MCMC_IS_FAITHFUL
@@ -380,7 +388,7 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
           // ---- item finished: the chain's state goes home (or, after the last iteration, to the outputs)
           if (it == B + S) {
             if (S == 0) acc = 0;  // reset after burn-in even when nothing is sampled (NUTS.py:494-500)
-            acc_total += (unsigned long long)acc;
+            acc_total += (unsigned int)acc;
             if (a.b.accept_count) a.b.accept_count[chain] = acc;
             if (a.b.accept_rate) a.b.accept_rate[chain] = (float)acc / (float)S;  // NUTS.py:512
             if (a.b.final_lp) a.b.final_lp[chain] = lpp;
@@ -447,10 +455,10 @@ __global__ void __launch_bounds__(BLOCK, DS > 0 ? kNutsMinBlocks : 1) nuts_kerne
   }
 #undef SLOT
   if (a.b.counters) {
-    if (acc_total) atomicAdd(a.b.counters + 0, acc_total);
-    if (n_grad) atomicAdd(a.b.counters + 1, n_grad);
-    if (sum_depth) atomicAdd(a.b.counters + 2, sum_depth);
-    if (n_div) atomicAdd(a.b.counters + 3, n_div);
+    if (acc_total) atomicAdd(a.b.counters + 0, (unsigned long long)acc_total);
+    if (n_grad) atomicAdd(a.b.counters + 1, (unsigned long long)n_grad);
+    if (sum_depth) atomicAdd(a.b.counters + 2, (unsigned long long)sum_depth);
+    if (n_div) atomicAdd(a.b.counters + 3, (unsigned long long)n_div);
   }
 }
 
